@@ -1,0 +1,82 @@
+// csi_internal.h -- host-side handle and the launch entry points of the two MLP engines.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/csi.h"
+#include "csi_net.cuh"
+
+namespace csi {
+
+// hidden-layer weight images for the tcgen05 engine (see csi_tc.cu for the layout)
+struct TcWeights {
+  const uint8_t *img;      // [n_steps][kLayerImageBytes]: fwd layers 1..5 then bwd layers 5..1
+  const float *small;      // packed fp32 parameters of the first / last layer, biases, scalings
+  int n_steps;
+  float act_scale, w_scale;  // power-of-two operand scalings (see csi_tc.cu)
+};
+
+struct Launch {           // everything a potential launch needs
+  DevModel model;
+  StarIO io;
+  NetDev emu, bcnet;
+  GridDev grid;
+  TcWeights tc;
+  double *partials;       // [grid][8]
+  unsigned int *counter;
+  double *out6;
+  float *grad_hyper;      // may be null
+  float *mean_out;        // predict mode only: [n][kMaxMean]
+  float *params_out;      // predict mode only: [n][8]
+  int sm_count;
+};
+
+// returns the number of kernel launches issued (>0) or a negative cudaError
+int launch_potential_ffma(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out);
+int launch_potential_tc(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out);
+int launch_predict_ffma(const Launch &L, cudaStream_t st);
+int launch_net_forward(const NetDev &net, const float *x, float *y, long long n, cudaStream_t st);
+int launch_net_vjp(const NetDev &net, const float *x, const float *gy, float *gx, long long n, cudaStream_t st);
+int launch_grid_forward(const GridDev &g, int bands, const float *x, float *y, long long n, cudaStream_t st);
+int launch_grid_vjp(const GridDev &g, int bands, const float *x, const float *gy, float *gx, long long n,
+                    cudaStream_t st);
+int max_partial_blocks(int sm_count, long long n);
+
+// host-side preparation of the tcgen05 weight images (csi_tc.cu)
+size_t tc_image_bytes(const csi_net &net);
+size_t tc_small_floats(const csi_net &net);
+void tc_build_images(const csi_net &net, uint8_t *img_host, float *small_host, float *act_scale, float *w_scale);
+bool tc_supported(const csi_net &net);
+
+}  // namespace csi
+
+struct csi_handle {
+  int device = 0, sm_count = 0, engine = 0;
+  int level = 0, prior = 0;
+  int n_hyper = 0, n_sites = 0;
+  int slot_of_site[csi::kSlots] = {0};
+  const char *names[CSI_MAX_HYPER + CSI_MAX_STAR_SITES] = {nullptr};
+  int rank = 0, world = 1;
+  csi::DevModel model{};
+  csi::NetDev emu{}, bcnet{};
+  csi::GridDev grid{};
+  csi::TcWeights tc{};
+  std::vector<void *> owned;  // device allocations released in csi_destroy
+  // data
+  long long n_local = 0;
+  float *d_obs = nullptr, *d_diag = nullptr, *d_mhloc = nullptr, *d_mhscale = nullptr, *d_mhlogz = nullptr;
+  bool has_diag = false, has_mh = false;
+  double *d_partials = nullptr;
+  unsigned int *d_counter = nullptr;
+  int partial_cap = 0;
+  // host-variant staging
+  float *h_z = nullptr, *h_grad = nullptr, *d_z = nullptr, *d_grad = nullptr;
+  double *h_out = nullptr, *d_out = nullptr;
+  long long stage_len = 0;
+  cudaStream_t stream = nullptr;
+  long long last_launches = 0;
+  int last_grid = 0, last_smem = 0;
+};
