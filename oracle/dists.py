@@ -49,7 +49,9 @@ def log_ndtr_diff(alpha, beta):
     """log(Phi(beta) - Phi(alpha)) for alpha < beta, stable in both tails; +-inf allowed.
 
     Returns (logZ, phi(alpha)/Z, phi(beta)/Z)."""
-    alpha, beta = np.broadcast_arrays(np.asarray(alpha, float), np.asarray(beta, float))
+    dt = np.result_type(np.asarray(alpha).dtype, np.asarray(beta).dtype)
+    dt = dt if dt == np.float32 else np.float64
+    alpha, beta = np.broadcast_arrays(np.asarray(alpha, dt), np.asarray(beta, dt))
     # mirror so that the mass sits in the lower tail whenever both bounds are positive
     flip = alpha > 0
     a = np.where(flip, -beta, alpha)

@@ -160,16 +160,19 @@ def _tn_logpdf_grads(x, mu, sigma, low, high):
 
 
 def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh_scale=None,
-                       return_terms=False):
+                       return_terms=False, dtype=np.float64):
     """U(z) = -(sum of site log-probs + log-Jacobians) and dU/dz for every site in ``z``.
 
     z: unconstrained values, scalars for hyper sites, shape [N] for per-star sites.
     obs, diag: [N, k] (k = number of observable columns; 'mag' expands to one column per band).
-    mh_loc / mh_scale: optional per-star M_H prior arrays (scripts/model_star.py:126-128)."""
+    mh_loc / mh_scale: optional per-star M_H prior arrays (scripts/model_star.py:126-128).
+    dtype: np.float64 (the oracle proper) or np.float32 -- every array operation in single precision, i.e. the
+    reference's DEFAULT precision (jax without --x64, scripts/model_star.py:73,86); used only to calibrate what
+    round-off an fp32 evaluation of this graph carries (tests/test_oracle_fp32_floor.py)."""
     c = spec.const
     emu = spec.emulator
     n = spec.num_stars
-    f64 = np.float64
+    f64 = np.dtype(dtype).type
     zz = {k: np.asarray(v, f64) for k, v in z.items()}
     obs = np.asarray(obs, f64).reshape(n, -1)
     diag = np.zeros_like(obs) if diag is None else np.broadcast_to(np.asarray(diag, f64), obs.shape)
@@ -223,6 +226,7 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
     dq_dmh = LN10 * q * (1.0 - q)
     g_mh_prior = 0.0                           # d(log prior)/d mh through mu_Y etc.
     extra = {}
+    extra_terms = {}
     if hier:
         # :318-333 -- decentred, bounds depend on (hyper, M_H); Y = mu + sigma*Y_dec = ylo + w*s
         f = dydz * q
@@ -248,6 +252,11 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
         g_ua = dl_da * da + (1 - 2 * sa)
         g_mua = np.sum(dl_dmua)
         g_siga = np.sum(dl_dsiga)
+        # conditioning of the five hyper-gradient sums: sum_i |contribution_i| in unconstrained units
+        extra_terms = dict(hyper_abs=np.array([
+            np.sum(np.abs(dl_dmu * dmu_dy0)), np.sum(np.abs(dl_dmu * dmu_df * q)) * abs(ddydz),
+            np.sum(np.abs(dl_dsig)) * 0.5 * sigma_y, np.sum(np.abs(dl_dmua)) * abs(dmu_a),
+            np.sum(np.abs(dl_dsiga)) * 0.5 * sigma_a], float))
     elif spec.prior == "flat":
         # :163-165 Uniform priors, interval transform
         y, dy, ldy, dldy = D.bounded_transform(zz["Y"], ylo, yhi)
@@ -309,12 +318,12 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
     # ---- predict (:203-218) -----------------------------------------------------------------
     x = np.stack([evol, mass, mh, y, a_mlt], axis=-1).astype(emu.dtype)
     out, masks = emu.forward(x, cache=True)
-    out = out.astype(f64) + c["delta"]["loc"]
-    mean = out @ A_MAT.T + C_VEC
+    out = out.astype(f64) + np.asarray(c["delta"]["loc"], f64)
+    mean = out @ A_MAT.T.astype(f64) + C_VEC.astype(f64)
     mean[:, 5] += log_mass
     mean[:, 6] += log_mass
     if spec.phot:
-        av = np.full(n, float(c["Av"]))
+        av = np.full(n, float(c["Av"]), f64)
         log_teff, log_g, log_l = mean[:, 1], mean[:, 5], mean[:, 4]
         if spec.bc_mode == "grid":      # _jax/star.py:40-44
             teff = 10.0 ** log_teff
@@ -334,16 +343,17 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
     r = obs - m
     g_mean = np.zeros_like(mean)
     if spec.kind == "diag":
-        s2 = spec.var_ext[idx] / tau[:, None] + diag
+        var_ext = spec.var_ext.astype(f64)
+        s2 = var_ext[idx] / tau[:, None] + diag
         ll = -0.5 * r * r / s2 - 0.5 * np.log(s2) - 0.5 * D.LOG_2PI
         g_m = r / s2
         dl_ds2 = 0.5 * r * r / s2 ** 2 - 0.5 / s2
-        g_tau = np.sum(dl_ds2 * (-spec.var_ext[idx] / tau[:, None] ** 2), axis=1)
+        g_tau = np.sum(dl_ds2 * (-var_ext[idx] / tau[:, None] ** 2), axis=1)
         ll = ll.sum(axis=1)
     else:
-        csub = spec.cov_ext[np.ix_(idx, idx)]
+        csub = spec.cov_ext[np.ix_(idx, idx)].astype(f64)
         k = len(idx)
-        S = csub[None] / tau[:, None, None] + diag[:, :, None] * np.eye(k)[None]
+        S = csub[None] / tau[:, None, None] + diag[:, :, None] * np.eye(k, dtype=f64)[None]
         L = np.linalg.cholesky(S)
         yv = np.linalg.solve(S, r[:, :, None])[:, :, 0]
         logdet = 2.0 * np.sum(np.log(np.diagonal(L, axis1=1, axis2=2)), axis=1)
@@ -358,7 +368,7 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
 
     # ---- reverse mode -------------------------------------------------------------------------
     g_logmass = g_mean[:, 5] + g_mean[:, 6]
-    g_mh = np.zeros(n)
+    g_mh = np.zeros(n, f64)
     if spec.phot:
         g_mag = g_mean[:, 7:7 + spec.bands]
         g_plx = g_mean[:, 7 + spec.bands]
@@ -370,7 +380,7 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
         g_mh = g_mh + g_bcin[:, 2]
         g_dist = g_mag.sum(axis=1) * 5.0 / (dist * LN10) - g_plx * 1e3 / dist ** 2
         g_usd = g_usd + g_dist * c["max_distance"] * sd * (1 - sd)
-    g_out = g_mean[:, :7] @ A_MAT
+    g_out = g_mean[:, :7] @ A_MAT.astype(f64)
     g_x = emu.vjp(masks, g_out.astype(emu.dtype)).astype(f64)
 
     grad = {}
@@ -395,7 +405,7 @@ def potential_and_grad(spec: ModelSpec, z: dict, obs, diag=None, mh_loc=None, mh
     per_star = lp_star + loglik
     u = -(logp + math.fsum(per_star.tolist()))
     if return_terms:
-        return u, grad, dict(mean=mean, per_star=per_star, hyper_logp=logp, x=x, out=out)
+        return u, grad, dict(mean=mean, per_star=per_star, hyper_logp=logp, x=x, out=out, **extra_terms)
     return u, grad
 
 

@@ -467,7 +467,8 @@ extern "C" int csi_predict(csi_handle *h, const float *z_dev, float *mean_dev, f
   Launch L;
   fill_launch(h, z_dev, nullptr, nullptr, L);
   L.mean_out = mean_dev; L.params_out = params_dev;
-  int rc = launch_predict_ffma(L, (cudaStream_t)stream);
+  int rc = h->engine == CSI_ENGINE_TCGEN05 ? launch_predict_tc(L, (cudaStream_t)stream)
+                                           : launch_predict_ffma(L, (cudaStream_t)stream);
   if (rc < 0) return fail(CSI_ECUDA, std::string("predict launch: ") + cudaGetErrorString((cudaError_t)(-rc)));
   return CSI_OK;
 }

@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(kRows) potential_ffma_kernel(const __grid_cons
     StarState st;
     star_pre(m, hv, io, i, st, acc);
     float o[4], g_o[4], g_x[8];
-    net_forward_ffma(L.emu, st.x, o, S.bufA, S.bufB, S.mask, tid);
+    float xin[8] = {st.x[0], st.x[1], st.x[2], st.x[3], st.x[4], 0.f, 0.f, 0.f};
+    net_forward_ffma(L.emu, xin, o, S.bufA, S.bufB, S.mask, tid);
     float *mean_out = nullptr;
     float mean_local[kMaxMean];
     if (PREDICT) mean_out = mean_local;
@@ -56,8 +57,10 @@ __global__ void __launch_bounds__(kRows) potential_ffma_kernel(const __grid_cons
     if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc, mean_out); }
     if (BC == 2) { BcNetFfma bc{L.bcnet, S.bufA, S.bufB, S.bcmask, tid}; star_mid(m, io, i, st, o, g_o, bc, mean_out); }
     if (PREDICT) {
-      if (L.mean_out)
+      if (L.mean_out) {
+#pragma unroll
         for (int k = 0; k < kMaxMean; ++k) L.mean_out[i * kMaxMean + k] = mean_local[k];
+      }
       if (L.params_out) {
         float *p = L.params_out + i * 8;
         p[0] = st.x[0]; p[1] = st.x[1]; p[2] = st.x[2]; p[3] = st.x[3]; p[4] = st.x[4];
@@ -126,15 +129,21 @@ __global__ void __launch_bounds__(kRows) net_kernel(const __grid_constant__ NetD
   const long long i = (long long)blockIdx.x * kRows + tid;
   if (i >= n) return;
   float xi[8], y[4];
-  for (int k = 0; k < net.n_in; ++k) xi[k] = x[i * net.n_in + k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) xi[k] = (k < net.n_in) ? x[i * net.n_in + k] : 0.0f;
   net_forward_ffma(net, xi, y, S.bufA, S.bufB, S.mask, tid);
   if (!VJP) {
-    for (int j = 0; j < net.n_out; ++j) out[i * net.n_out + j] = y[j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (j < net.n_out) out[i * net.n_out + j] = y[j];
   } else {
     float g[4], gx[8];
-    for (int j = 0; j < net.n_out; ++j) g[j] = gy[i * net.n_out + j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) g[j] = (j < net.n_out) ? gy[i * net.n_out + j] : 0.0f;
     net_vjp_ffma(net, g, gx, S.bufA, S.bufB, S.mask, tid);
-    for (int k = 0; k < net.n_in; ++k) out[i * net.n_in + k] = gx[k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (k < net.n_in) out[i * net.n_in + k] = gx[k];
   }
 }
 

@@ -38,6 +38,7 @@ struct Launch {           // everything a potential launch needs
 int launch_potential_ffma(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out);
 int launch_potential_tc(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out);
 int launch_predict_ffma(const Launch &L, cudaStream_t st);
+int launch_predict_tc(const Launch &L, cudaStream_t st);
 int launch_net_forward(const NetDev &net, const float *x, float *y, long long n, cudaStream_t st);
 int launch_net_vjp(const NetDev &net, const float *x, const float *gy, float *gx, long long n, cudaStream_t st);
 int launch_grid_forward(const GridDev &g, int bands, const float *x, float *y, long long n, cudaStream_t st);

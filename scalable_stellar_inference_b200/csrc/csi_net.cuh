@@ -78,10 +78,14 @@ CSI_DEV void dense_ffma(const float *__restrict__ in, float *__restrict__ out, c
 // words of mask storage per hidden layer
 CSI_DEV int mask_words(const NetDev &net) { return (net.n_hidden + 31) >> 5; }
 
-// forward: x[n_in] (registers) -> y[n_out]; bufA/bufB thread-private smem columns; masks recorded.
+// forward: x[8] (registers, first n_in used) -> y[4]; bufA/bufB thread-private smem columns; masks recorded.
 CSI_DEV void net_forward_ffma(const NetDev &net, const float *x, float *y, float *bufA, float *bufB,
                               uint32_t *mask, int tid) {
-  for (int k = 0; k < net.n_in; ++k) bufA[k * kRows + tid] = (x[k] - net.in_loc[k]) / net.in_scale[k];
+  // fixed-trip, guarded loops: x / y stay in registers (a runtime-bounded loop over a caller's local array
+  // made nvcc 12.9 drop the stores to y in the forward-only instantiation)
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (k < net.n_in) bufA[k * kRows + tid] = (x[k] - net.in_loc[k]) / net.in_scale[k];
   float *a = bufA, *b = bufB;
   const int mw = mask_words(net);
   const int L = net.n_layers;
@@ -90,15 +94,18 @@ CSI_DEV void net_forward_ffma(const NetDev &net, const float *x, float *y, float
     float *t = a; a = b; b = t;
   }
   dense_ffma<0>(a, b, net.W[L - 1], net.b[L - 1], net.kdim[L - 1], net.np[L - 1], nullptr, tid);
-  for (int j = 0; j < net.n_out; ++j) y[j] = net.out_loc[j] + net.out_scale[j] * b[j * kRows + tid];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) y[j] = (j < net.n_out) ? net.out_loc[j] + net.out_scale[j] * b[j * kRows + tid] : 0.0f;
 }
 
-// input-VJP: g_y[n_out] -> g_x[n_in], using the masks recorded by net_forward_ffma
+// input-VJP: g_y[4] -> g_x[8], using the masks recorded by net_forward_ffma
 CSI_DEV void net_vjp_ffma(const NetDev &net, const float *g_y, float *g_x, float *bufA, float *bufB,
                           uint32_t *mask, int tid) {
   const int L = net.n_layers;
   const int mw = mask_words(net);
-  for (int j = 0; j < net.n_out; ++j) bufA[j * kRows + tid] = g_y[j] * net.out_scale[j];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (j < net.n_out) bufA[j * kRows + tid] = g_y[j] * net.out_scale[j];
   float *a = bufA, *b = bufB;
   for (int l = L - 1; l >= 1; --l) {
     // g_in[k] = sum_j g_out[j] W[k][j]  -> "K" = ndim[l], out width = kp[l]; then ReLU mask of layer l-1
@@ -106,7 +113,8 @@ CSI_DEV void net_vjp_ffma(const NetDev &net, const float *g_y, float *g_x, float
     float *t = a; a = b; b = t;
   }
   dense_ffma<0>(a, b, net.Wt[0], nullptr, net.ndim[0], net.kp[0], nullptr, tid);
-  for (int k = 0; k < net.n_in; ++k) g_x[k] = b[k * kRows + tid] / net.in_scale[k];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) g_x[k] = (k < net.n_in) ? b[k * kRows + tid] / net.in_scale[k] : 0.0f;
 }
 
 // BC emulator as a BC source for star_mid (FFMA engine): forward then VJP on the same buffers
@@ -117,7 +125,8 @@ struct BcNetFfma {
   int tid;
   CSI_DEV void forward(const float in[4], float val[4]) {
     float y[4] = {0.f, 0.f, 0.f, 0.f};
-    net_forward_ffma(net, in, y, bufA, bufB, mask, tid);
+    const float x8[8] = {in[0], in[1], in[2], in[3], 0.f, 0.f, 0.f, 0.f};
+    net_forward_ffma(net, x8, y, bufA, bufB, mask, tid);
 #pragma unroll
     for (int b = 0; b < 4; ++b) val[b] = y[b];
   }

@@ -8,7 +8,7 @@
 //
 // with every fp32 operand split into an fp16 (hi, lo) pair and three MMA passes
 //   A_lo*B_hi + A_hi*B_lo + A_hi*B_hi          (fp32 accumulate in TMEM)
-// which keeps ~22 significant bits per operand -- the parity bar is the reference's fp32 CPU path, which
+// which keeps ~23 significant bits per operand -- the parity bar is the reference's fp32 CPU path, which
 // single-pass TF32/BF16/FP16 misses by 3 orders of magnitude (DESIGN.md "precision").  Operands are scaled
 // by powers of two into the fp16 range (activations: fixed scale; cotangents: per-row scale), so the
 // splitting is exact up to the dropped lo*lo term.
@@ -77,12 +77,12 @@ __host__ __device__ constexpr uint32_t img_offset(int n, int k) {
          (uint32_t)(n & 7) * 16 + (uint32_t)(k & 7) * 2;
 }
 
-// fp32 -> (hi, lo) fp16 pair: hi = 11 leading bits (truncation, exact in fp16), lo = rn(v - hi)
+// fp32 -> (hi, lo) fp16 pair: hi = rn16(v), lo = rn16(v - hi) (v - hi is exact in fp32); round-to-nearest on
+// both halves keeps 23 significant bits and leaves the dropped lo*lo term without a preferred sign
 __device__ __forceinline__ void split2(float v0, float v1, uint32_t &hi, uint32_t &lo) {
-  float h0 = __uint_as_float(__float_as_uint(v0) & 0xFFFFE000u);
-  float h1 = __uint_as_float(__float_as_uint(v1) & 0xFFFFE000u);
-  __half2 hh = __floats2half2_rn(h0, h1);
-  __half2 ll = __floats2half2_rn(v0 - h0, v1 - h1);
+  __half2 hh = __floats2half2_rn(v0, v1);
+  float2 hf = __half22float2(hh);
+  __half2 ll = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
   hi = *reinterpret_cast<uint32_t *>(&hh);
   lo = *reinterpret_cast<uint32_t *>(&ll);
 }
@@ -96,8 +96,10 @@ __device__ __forceinline__ void store_a_chunk(uint32_t a_base, int c, const floa
   ptx::tmem_st16(a_base + 64 + 16 * c, lo);
 }
 
-template <int BC>
+// PREDICT = forward only (5 steps): writes predict's means / parameters instead of gradients (csi_predict).
+template <int BC, bool PREDICT>
 __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_constant__ Launch L) {
+  constexpr int kNSteps = PREDICT ? 5 : kSteps;
   extern __shared__ unsigned char smem_raw[];
   Smem &S = *reinterpret_cast<Smem *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const DevModel &m = L.model;
@@ -134,10 +136,10 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   if (warp == 9) {
     // ===== weight loader: stream the 64 KB image of every step into the 2-deep ring ====================
     if (lane == 0) {
-      const long long total = my_pairs * kSteps;
+      const long long total = my_pairs * kNSteps;
       for (long long it = 0; it < total; ++it) {
         const int buf = (int)(it & 1);
-        const int step = (int)(it % kSteps);
+        const int step = (int)(it % kNSteps);
         ptx::mbar_wait(&S.w_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
         ptx::mbar_arrive_expect_tx(&S.w_full[buf], kStepBytes);
         const uint8_t *src = L.tc.img + (size_t)step * kStepBytes;
@@ -150,7 +152,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   } else if (warp == 8) {
     // ===== MMA issuer ===============================================================================
     const uint32_t idesc = ptx::make_idesc_f16(128, 128);
-    const long long total = my_pairs * kSteps;
+    const long long total = my_pairs * kNSteps;
     for (long long it = 0; it < total; ++it) {
       const int buf = (int)(it & 1);
       ptx::mbar_wait(&S.w_full[buf], (uint32_t)((it >> 1) & 1));
@@ -240,7 +242,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       float g_o[4] = {0.f, 0.f, 0.f, 0.f};
       float un = 1.0f;  // cotangent un-scaling: true value = D * un
 #pragma unroll 1
-      for (int step = 0; step < kSteps; ++step, ++it) {
+      for (int step = 0; step < kNSteps; ++step, ++it) {
         ptx::mbar_wait(&S.d_ready[t], (uint32_t)(it & 1));
         ptx::tc_fence_after();
         if (step < 4) {
@@ -290,11 +292,25 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             float o[4];
 #pragma unroll
             for (int c = 0; c < 4; ++c) o[c] = sm[oOutLoc + c] + sm[oOutScale + c] * y[c];
-            if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc); }
-            if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc); }
+            float mean_local[kMaxMean];
+            float *mo = PREDICT ? mean_local : nullptr;
+            if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, mo); }
+            if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc, mo); }
 #pragma unroll
             for (int c = 0; c < 4; ++c) g_y[c] = g_o[c] * sm[oOutScale + c];
+            if (PREDICT) {
+              if (L.mean_out) {
+#pragma unroll
+                for (int k = 0; k < kMaxMean; ++k) L.mean_out[i * kMaxMean + k] = mean_local[k];
+              }
+              if (L.params_out) {
+                float4 *p = reinterpret_cast<float4 *>(L.params_out + i * 8);
+                p[0] = make_float4(st.x[0], st.x[1], st.x[2], st.x[3]);
+                p[1] = make_float4(st.x[4], st.log_mass, st.tau, st.dist);
+              }
+            }
           }
+          if (!PREDICT) {
           // per-row power-of-two scale from a bound on |g_y W6^T|
           float bound = fabsf(g_y[0]) * sm[oW6Max] + fabsf(g_y[1]) * sm[oW6Max + 1] + fabsf(g_y[2]) * sm[oW6Max + 2] +
                         fabsf(g_y[3]) * sm[oW6Max + 3];
@@ -317,6 +333,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             }
             store_a_chunk(a_base, c, v);
           }
+          }  // !PREDICT
         } else if (step < 9) {
           // ---- cotangent of hidden layer h = 9 - step: ReLU mask, re-scale, next A operand ----------------
           const int h = 9 - step;
@@ -373,7 +390,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             acc.lp += (double)st.lp;
           }
         }
-        if (step < 9) {
+        if (step < kNSteps - 1) {
           ptx::tmem_wait_st();
           ptx::tc_fence_before();
           ptx::mbar_arrive(&S.a_ready[t]);
@@ -389,7 +406,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);
-  block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
+  if (!PREDICT) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
 }
 
 }  // namespace tc
@@ -430,12 +447,10 @@ void tc_build_images(const csi_net &net, uint8_t *img, float *small, float *act_
       for (int k = 0; k < kHid; ++k) {
         // forward: B[n = out][k = in] = W[k][n];  transposed: B[n = in][k = out] = W[n][k]
         const float w = (fwd ? W[(size_t)k * kHid + nn] : W[(size_t)nn * kHid + k]) * s;
-        uint32_t u;
-        std::memcpy(&u, &w, 4);
-        u &= 0xFFFFE000u;
-        float h;
-        std::memcpy(&h, &u, 4);
-        const uint16_t hb = half_bits(h), lb = half_bits(w - h);
+        const uint16_t hb = half_bits(w);
+        __half hh;
+        std::memcpy(&hh, &hb, 2);
+        const uint16_t lb = half_bits(w - __half2float(hh));
         const uint32_t off = img_offset(nn, k);
         std::memcpy(hi + off, &hb, 2);
         std::memcpy(lo + off, &lb, 2);
@@ -465,10 +480,10 @@ void tc_build_images(const csi_net &net, uint8_t *img, float *small, float *act_
   }
 }
 
-template <int BC>
+template <int BC, bool PREDICT>
 static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out) {
   const int smem = (int)sizeof(tc::Smem) + 1024;
-  auto kern = tc::potential_tc_kernel<BC>;
+  auto kern = tc::potential_tc_kernel<BC, PREDICT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return -(int)e;
   const long long n_tiles = (L.io.n + tc::kTile - 1) / tc::kTile;
@@ -483,8 +498,13 @@ static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *sme
 }
 
 int launch_potential_tc(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out) {
-  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1>(L, st, grid_out, smem_out);
-  return launch_tc_t<0>(L, st, grid_out, smem_out);
+  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, false>(L, st, grid_out, smem_out);
+  return launch_tc_t<0, false>(L, st, grid_out, smem_out);
+}
+
+int launch_predict_tc(const Launch &L, cudaStream_t st) {
+  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, true>(L, st, nullptr, nullptr);
+  return launch_tc_t<0, true>(L, st, nullptr, nullptr);
 }
 
 }  // namespace csi

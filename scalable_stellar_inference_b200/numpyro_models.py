@@ -301,6 +301,7 @@ class SingleStarModel:
         finally:
             for p in ptrs:
                 lib.csi_dev_free(h, p)
+        self._last_mean = mean
         d = {nm: mean[:, i] for i, nm in enumerate(self.output_names)}
         for i, nm in enumerate(["evol", "mass", "M_H", "Y", "a_MLT", "log_mass", "scaled_precision"]):
             d[nm] = par[:, i]
