@@ -2,6 +2,7 @@
 // and the stream-ordered evaluation entry points.  No CPU fallback: creation fails without an sm_100 device.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -225,6 +226,20 @@ static int upload_grid(csi_handle *h, const csi_grid &g, int bands, GridDev &d) 
     float *dp; int rc;
     if ((rc = dev_upload(h, p, &dp))) return rc;
     d.pts[a] = dp;
+    // uniform-bin lookup table over [p0, p_last]: lut[b] = (number of points < left edge of bin b) - 1, in [0, n-2]
+    if (g.shape[a] > 65535) return fail(CSI_EINVAL, "bc_grid: axis too long");
+    const float x0 = p.front(), x1 = p.back();
+    const float inv = (float)kLutBins / (x1 - x0);
+    std::vector<unsigned short> lut(kLutBins);
+    for (int b = 0; b < kLutBins; ++b) {
+      const float edge = x0 + (float)b / inv;
+      int cnt = 0;
+      while (cnt < g.shape[a] && p[cnt] < edge) ++cnt;
+      lut[b] = (unsigned short)std::min(std::max(cnt - 1, 0), g.shape[a] - 2);
+    }
+    unsigned short *dl;
+    if ((rc = dev_upload(h, lut, &dl))) return rc;
+    d.lut[a] = dl; d.lut_x0[a] = x0; d.lut_inv[a] = inv;
   }
   if (!g.values) return fail(CSI_EINVAL, "bc_grid: null values");
   std::vector<float4> v(nn);
@@ -281,18 +296,28 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
   if (rc == CSI_OK && cfg->engine != CSI_ENGINE_TCGEN05 && cfg->engine != CSI_ENGINE_FFMA)
     rc = fail(CSI_EINVAL, "unknown engine");
   if (rc == CSI_OK && cfg->engine == CSI_ENGINE_TCGEN05) {
-    if (!tc_supported(cfg->emulator)) rc = fail(CSI_EINVAL, "tcgen05 engine needs the 5->128x6->4 emulator");
+    if (!tc_supported(cfg->emulator)) rc = fail(CSI_EINVAL, "tcgen05 engine needs the 5->128x6->4 emulator with biases within 64x the largest weight");
     else if (cfg->bands > 0 && cfg->bc_mode == CSI_BC_NET)
       rc = fail(CSI_EINVAL, "tcgen05 engine: BC-emulator net inside the potential is not supported yet; use "
                             "CSI_ENGINE_FFMA or the BC table");
     else {
-      std::vector<uint8_t> img(tc_image_bytes(cfg->emulator));
+      std::vector<uint8_t> img(tc_image_bytes(cfg->emulator)), resident(tc_resident_bytes(cfg->emulator));
       std::vector<float> small(tc_small_floats(cfg->emulator));
-      tc_build_images(cfg->emulator, img.data(), small.data(), &h->tc.act_scale, &h->tc.w_scale);
-      uint8_t *di; float *ds;
+      tc_build_images(cfg->emulator, img.data(), resident.data(), small.data(), &h->tc.act_scale, &h->tc.w_scale);
+      uint8_t *di, *dr; float *ds;
       rc = dev_upload(h, img, &di);
+      if (rc == CSI_OK) rc = dev_upload(h, resident, &dr);
       if (rc == CSI_OK) rc = dev_upload(h, small, &ds);
-      if (rc == CSI_OK) { h->tc.img = di; h->tc.small = ds; h->tc.n_steps = 2 * (cfg->emulator.n_layers - 2); }
+      if (rc == CSI_OK) {
+        h->tc.debug = getenv("CSI_TC_DEBUG") ? atoi(getenv("CSI_TC_DEBUG")) : 0;
+        if (h->tc.debug & 8) {
+          std::vector<long long> z(8 * 1024, 0);
+          long long *dt;
+          rc = dev_upload(h, z, &dt);
+          h->tc.trace = dt;
+        }
+        h->tc.img = di; h->tc.resident = dr; h->tc.small = ds; h->tc.n_steps = 2 * (cfg->emulator.n_layers - 2);
+      }
     }
   }
   if (rc == CSI_OK) {
@@ -542,6 +567,13 @@ extern "C" int csi_synchronize(csi_handle *h) {
   if (!h) return fail(CSI_EINVAL, "null handle");
   CK(cudaSetDevice(h->device));
   CK(cudaDeviceSynchronize());
+  return CSI_OK;
+}
+
+// debugging aid (not part of the public header): copies the clock64 trace of CTA 0 recorded under CSI_TC_DEBUG=8
+extern "C" int csi_tc_trace(csi_handle *h, long long *out, int n) {
+  if (!h || !h->tc.trace) return fail(CSI_ESTATE, "no trace");
+  CK(cudaMemcpy(out, h->tc.trace, sizeof(long long) * n, cudaMemcpyDeviceToHost));
   return CSI_OK;
 }
 

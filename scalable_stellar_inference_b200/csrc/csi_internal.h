@@ -13,9 +13,12 @@ namespace csi {
 
 // hidden-layer weight images for the tcgen05 engine (see csi_tc.cu for the layout)
 struct TcWeights {
-  const uint8_t *img;      // [n_steps][kLayerImageBytes]: fwd layers 1..5 then bwd layers 5..1
-  const float *small;      // packed fp32 parameters of the first / last layer, biases, scalings
+  const uint8_t *img;      // [10][kStepBytes]: streamed images, fwd layers 1..5 then transposed layers 5..1
+  const uint8_t *resident; // images of the four narrow stages (layer 0, 6, 6^T, 0^T), kept in shared memory
+  const float *small;      // packed fp32 scalings / gains
   int n_steps;
+  long long *trace;        // CSI_TC_DEBUG & 8: clock64 trace of CTA 0 (csi_tc_trace)
+  int debug;               // CSI_TC_DEBUG experiments (timing only; results are wrong when non-zero)
   float act_scale, w_scale;  // power-of-two operand scalings (see csi_tc.cu)
 };
 
@@ -48,8 +51,10 @@ int max_partial_blocks(int sm_count, long long n);
 
 // host-side preparation of the tcgen05 weight images (csi_tc.cu)
 size_t tc_image_bytes(const csi_net &net);
+size_t tc_resident_bytes(const csi_net &net);
 size_t tc_small_floats(const csi_net &net);
-void tc_build_images(const csi_net &net, uint8_t *img_host, float *small_host, float *act_scale, float *w_scale);
+void tc_build_images(const csi_net &net, uint8_t *img_host, uint8_t *resident_host, float *small_host,
+                     float *act_scale, float *w_scale);
 bool tc_supported(const csi_net &net);
 
 }  // namespace csi

@@ -71,9 +71,12 @@ struct StarIO {
 };
 
 // 4-D BC table, float4-padded bands
+constexpr int kLutBins = 256;
 struct GridDev {
   int shape[4];
   const float *pts[4];
+  const unsigned short *lut[4];  // [kLutBins] per axis: an interval index <= the answer for every x of the bin
+  float lut_x0[4], lut_inv[4];   // bin = (x - lut_x0) * lut_inv
   const float4 *values;  // [n0*n1*n2*n3]
 };
 
@@ -224,27 +227,31 @@ struct HyperAcc {  // per-thread partial sums of dlogp/d(y0, dydz, sigma_y, mu_a
 CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, long long i, StarState &st,
                       HyperAcc &acc) {
   float lp = 0.0f;
+  // every input of this star first: independent global loads in flight together
+  float zv[kSlots];
+#pragma unroll
+  for (int s = 0; s < kSlots; ++s) zv[s] = io.z[s] ? io.z[s][i] : 0.0f;
+  const float mloc = io.mh_loc ? io.mh_loc[i] : m.mh.loc;
+  const float mscale = io.mh_scale ? io.mh_scale[i] : m.mh.scale;
+  const float mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.logz;
 #pragma unroll
   for (int s = 0; s < kSlots; ++s) st.gp[s] = 0.0f;
   // scaled_precision ~ Gamma(df/2, df/2)   (:195-196 / :301-302)
   float lt, dlt;
-  gamma_site(io.z[S_TAU][i], m.tau_conc, m.tau_rate, m.tau_const, st.tau, lt, dlt);
+  gamma_site(zv[S_TAU], m.tau_conc, m.tau_rate, m.tau_const, st.tau, lt, dlt);
   lp += lt; st.gp[S_TAU] = dlt;
   // log_evol, log_mass, M_H: constant-bound truncated normals (:149-161 / :304-316)
   float v, dv;
-  tn_site(m.log_evol, io.z[S_EVOL][i], m.log_evol.loc, m.log_evol.scale, m.log_evol.logz, v, dv, lt, dlt);
+  tn_site(m.log_evol, zv[S_EVOL], m.log_evol.loc, m.log_evol.scale, m.log_evol.logz, v, dv, lt, dlt);
   lp += lt; st.gp[S_EVOL] = dlt;
   float evol = exp10f(v);
   st.x[0] = evol; st.c_evol = kLn10 * evol * dv;
-  tn_site(m.log_mass, io.z[S_MASS][i], m.log_mass.loc, m.log_mass.scale, m.log_mass.logz, v, dv, lt, dlt);
+  tn_site(m.log_mass, zv[S_MASS], m.log_mass.loc, m.log_mass.scale, m.log_mass.logz, v, dv, lt, dlt);
   lp += lt; st.gp[S_MASS] = dlt;
   float mass = exp10f(v);
   st.log_mass = v; st.x[1] = mass; st.c_mass = kLn10 * mass * dv; st.dlm = dv;
-  float mloc = io.mh_loc ? io.mh_loc[i] : m.mh.loc;
-  float mscale = io.mh_scale ? io.mh_scale[i] : m.mh.scale;
-  float mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.logz;
   float mh;
-  tn_site(m.mh, io.z[S_MH][i], mloc, mscale, mlogz, mh, dv, lt, dlt);
+  tn_site(m.mh, zv[S_MH], mloc, mscale, mlogz, mh, dv, lt, dlt);
   lp += lt; st.gp[S_MH] = dlt;
   st.x[2] = mh; st.dmh = dv;
 
@@ -260,7 +267,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     float mu_y = (h.y0 + f) * inv1f;
     float dmu_dy0 = inv1f;
     float dmu_df = (1.0f - h.y0) * inv1f * inv1f;
-    float uy = io.z[S_Y][i];
+    float uy = zv[S_Y];
     float sy = sigmoidf_(uy);
     float y = m.y_lo + m.y_w * sy;
     float dy = m.y_w * sy * (1.0f - sy);
@@ -273,7 +280,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     acc.g[1] += (double)(dl_dmu * dmu_df * q);
     acc.g[2] += (double)dl_dsig;
     st.x[3] = y; st.dy = dy;
-    float ua = io.z[S_A][i];
+    float ua = zv[S_A];
     float sa = sigmoidf_(ua);
     float a = m.a_lo + m.a_w * sa;
     float da = m.a_w * sa * (1.0f - sa);
@@ -285,7 +292,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     acc.g[4] += (double)dl_dsiga;
     st.x[4] = a; st.da = da;
   } else {
-    float uy = io.z[S_Y][i], ua = io.z[S_A][i];
+    float uy = zv[S_Y], ua = zv[S_A];
     float sy = sigmoidf_(uy), sa = sigmoidf_(ua);
     float y = m.y_lo + m.y_w * sy, a = m.a_lo + m.a_w * sa;
     float dy = m.y_w * sy * (1.0f - sy), da = m.a_w * sa * (1.0f - sa);
@@ -299,7 +306,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     } else {
       // informative (:167-193): per-star precision sites; enrichment-law uncertainty folded in
       float py, pa;
-      gamma_site(io.z[S_PY][i], m.py_conc, m.py_rate, m.py_const, py, lt, dlt);
+      gamma_site(zv[S_PY], m.py_conc, m.py_rate, m.py_const, py, lt, dlt);
       lp += lt; float g_upy = dlt;
       float sig_y0sq = 1.0f / py;
       float zxp1 = t + 1.0f;
@@ -322,7 +329,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
       float dsig = (f_dydz * s1 * s1 * dfd + f_y0 * s0 * s0 * dfy) / sig_yt;
       g_mh_prior += dl_dmu * dmu + dl_dsig * dsig;
       st.gp[S_PY] = g_upy + dl_dsig * (-0.5f * sig_y0sq / sig_yt);
-      gamma_site(io.z[S_PA][i], m.pa_conc, m.pa_rate, m.pa_const, pa, lt, dlt);
+      gamma_site(zv[S_PA], m.pa_conc, m.pa_rate, m.pa_const, pa, lt, dlt);
       lp += lt; float g_upa = dlt;
       float sig_a0sq = 1.0f / pa;
       float sig_at = sqrtf(sig_a0sq + m.inf_mua_scale * m.inf_mua_scale);
@@ -338,7 +345,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
   st.dist = 1.0f; st.dsd = 0.0f;
   if (m.bands > 0) {
     // scaled_distance ~ Beta(c1, c0) on (0,1), sigmoid transform (notebook/single-star-phot.ipynb cell [7])
-    float u = io.z[S_SD][i];
+    float u = zv[S_SD];
     float sd = sigmoidf_(u);
     lp += m.sd_const + (m.sd_c1 - 1.0f) * logf(sd) + (m.sd_c0 - 1.0f) * log1pf(-sd) + log_sigmoid_prod(u);
     st.gp[S_SD] = m.sd_c1 * (1.0f - sd) - m.sd_c0 * sd;
@@ -352,18 +359,20 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
 // ---------------------------------------------------------------------------------------------
 // BC table: multilinear interpolation with analytic Jacobian (jax.scipy RegularGridInterpolator, linear)
 // ---------------------------------------------------------------------------------------------
-CSI_DEV int grid_locate(const float *__restrict__ g, int n, float x, float &t, float &inv_w, bool &oob) {
-  // searchsorted(g, x, 'left') - 1, clipped to [0, n-2]
-  int lo = 0, hi = n;  // first index with g[idx] >= x
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (__ldg(g + mid) < x) lo = mid + 1; else hi = mid;
-  }
-  int i = min(max(lo - 1, 0), n - 2);
-  float g0 = __ldg(g + i), g1 = __ldg(g + i + 1);
+// searchsorted(g, x, 'left') - 1, clipped to [0, n-2]: the largest i with g[i] < x.  A uniform-bin lookup table
+// gives a start index that is never past the answer (one bin of slack absorbs the rounding of the bin number);
+// a short linear walk finishes.  Pointers may be global or shared (the tcgen05 kernel keeps the axes in smem).
+CSI_DEV int grid_locate(const float *g, const unsigned short *lut, float x0, float inv_bin, int n, float x, float &t,
+                        float &inv_w, bool &oob) {
+  int b = (int)((x - x0) * inv_bin) - 1;
+  b = min(max(b, 0), kLutBins - 1);
+  int i = (x == x) ? (int)lut[b] : 0;
+  float g1 = g[i + 1];
+  while (i < n - 2 && g1 < x) { ++i; g1 = g[i + 1]; }
+  const float g0 = g[i];
   inv_w = 1.0f / (g1 - g0);
   t = (x - g0) * inv_w;
-  oob = oob || (x < __ldg(g)) || (x > __ldg(g + n - 1)) || !(x == x);
+  oob = oob || (x < g[0]) || (x > g[n - 1]) || !(x == x);
   return i;
 }
 
@@ -371,7 +380,8 @@ CSI_DEV int grid_locate(const float *__restrict__ g, int n, float x, float &t, f
 CSI_DEV void grid_eval(const GridDev &gd, const float x[4], float val[4], float jac[4][4]) {
   int idx[4]; float t[4], iw[4]; bool oob = false;
 #pragma unroll
-  for (int d = 0; d < 4; ++d) idx[d] = grid_locate(gd.pts[d], gd.shape[d], x[d], t[d], iw[d], oob);
+  for (int d = 0; d < 4; ++d)
+    idx[d] = grid_locate(gd.pts[d], gd.lut[d], gd.lut_x0[d], gd.lut_inv[d], gd.shape[d], x[d], t[d], iw[d], oob);
   const long long s3 = 1, s2 = gd.shape[3], s1 = s2 * gd.shape[2], s0 = s1 * gd.shape[1];
   const float4 *base = gd.values + idx[0] * s0 + idx[1] * s1 + idx[2] * s2 + idx[3] * s3;
   float4 c[16];
@@ -415,6 +425,14 @@ CSI_DEV void grid_eval(const GridDev &gd, const float x[4], float val[4], float 
 template <class BcFn>
 CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarState &st, const float o[4],
                       float g_o[4], BcFn &&bc, float *mean_out = nullptr) {
+  // observations first: independent loads in flight while the bolometric corrections are gathered
+  float ob_[kMaxObs], dg_[kMaxObs];
+#pragma unroll
+  for (int a = 0; a < kMaxObs; ++a) {
+    const bool on = a < m.n_obs;
+    ob_[a] = on ? io.obs[a][i] : 0.0f;
+    dg_[a] = (on && io.diag[a]) ? io.diag[a][i] : 0.0f;
+  }
   float mean[kMaxMean];
   // loc = A @ (o + delta_loc) + B @ params + c
   mean[0] = o[0] + m.cc[0];
@@ -458,8 +476,10 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
     for (int k = 0; k < kMaxMean; ++k) {
       int col = m.col_of_mean[k];
       if (col >= 0) {
-        float ob = io.obs[col][i];
-        float dg = io.diag[col] ? io.diag[col][i] : 0.0f;
+        float ob = 0.0f, dg = 0.0f;
+#pragma unroll
+        for (int a = 0; a < kMaxObs; ++a)
+          if (a == col) { ob = ob_[a]; dg = dg_[a]; }
         float vk = m.var_ext[k] * inv_tau;
         float s2 = vk + dg;
         float inv_s2 = 1.0f / s2;
@@ -477,8 +497,11 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
     float S[kMaxObs * kMaxObs], r[kMaxObs], yv[kMaxObs];
     for (int a = 0; a < k; ++a) {
       int ia = m.obs_idx[a];
-      float dg = io.diag[a] ? io.diag[a][i] : 0.0f;
-      r[a] = io.obs[a][i] - mean[ia];
+      float dg = 0.0f, oba = 0.0f;
+#pragma unroll
+      for (int a2 = 0; a2 < kMaxObs; ++a2)
+        if (a2 == a) { dg = dg_[a2]; oba = ob_[a2]; }
+      r[a] = oba - mean[ia];
       for (int b = 0; b < k; ++b)
         S[a * kMaxObs + b] = m.cov_ext[ia * kMaxMean + m.obs_idx[b]] * inv_tau + (a == b ? dg : 0.0f);
     }

@@ -2,26 +2,36 @@
 // -> gradient stores -> reduction) as ONE persistent kernel for sm_100a.
 //
 // Tile = 128 stars = the 128 TMEM lanes; a thread of an "epilogue" warpgroup owns one star end to end.
-// The five hidden 128x128 layers (forward) and their transposes (VJP) run on the tensor cores:
+// ALL SEVEN layers of the emulator and ALL SEVEN transposed layers of its input-VJP run on the tensor cores:
 //
-//   D[128 x 128] (TMEM, fp32)  =  A[128 x 128] (TMEM, fp16)  x  B[128 x 128] (smem, fp16, K-major)
+//   D[128 x N] (TMEM, fp32)  =  A[128 x K] (TMEM, fp16)  x  B[N x K] (smem, fp16, K-major)
 //
-// with every fp32 operand split into an fp16 (hi, lo) pair and three MMA passes
-//   A_lo*B_hi + A_hi*B_lo + A_hi*B_hi          (fp32 accumulate in TMEM)
+// with every fp32 operand split into an fp16 (hi, lo) pair and three products per contraction
+//   A_lo*B_hi + A_hi*B_lo + A_hi*B_hi          (fp32 accumulate in TMEM, small terms first)
 // which keeps ~23 significant bits per operand -- the parity bar is the reference's fp32 CPU path, which
 // single-pass TF32/BF16/FP16 misses by 3 orders of magnitude (DESIGN.md "precision").  Operands are scaled
 // by powers of two into the fp16 range (activations: fixed scale; cotangents: per-row scale), so the
-// splitting is exact up to the dropped lo*lo term.
+// splitting is exact up to the dropped lo*lo term.  Forward biases are folded into the contraction (constant
+// A entries x a 3-term fp16 split of the bias), so the epilogue never adds them.
 //
-// Activations never leave the SM: the epilogue reads D with tcgen05.ld, applies bias / ReLU / mask,
-// splits, and writes the next layer's A operand straight back to TMEM with tcgen05.st.  ReLU masks are
-// 6 x 128 bits per star held in registers.  The first (5->128) and last (128->4) layers, the priors, the
-// BC table gather and the likelihood run on the CUDA cores of the same thread.
+// Stages of one tile (MMA -> epilogue), 14 per evaluation:
+//    0      layer 0   (5 -> 128):   K = 32  [x_hi | x_lo | x_hi | c c c] x [W0_hi; W0_hi; W0_lo; bias split]
+//    1..5   layers 1..5 (128 -> 128): 24 MMAs + 1 bias MMA, weights streamed (ring)
+//    6      layer 6   (128 -> 4):   N = 16, 24 MMAs + bias; epilogue = likelihood + cotangent of the outputs
+//    7      layer 6^T (4 -> 128):   K = 16  [g_hi | g_lo | g_hi | 0] x [W6_hi; W6_hi; W6_lo; 0]
+//    8..12  layers 5..1 transposed, weights streamed (ring)
+//    13     layer 0^T (128 -> 5):   N = 16, 24 MMAs; epilogue = chain rule to the sites + gradient stores
+// Activations never leave the SM: the epilogue reads D with tcgen05.ld, applies ReLU / mask, splits, and
+// writes the next stage's A operand straight back to TMEM with tcgen05.st.  ReLU masks are the SIGN bits of
+// the pre-activations, 6 x 128 bits per star, gathered with one funnel shift per element and applied in the
+// VJP with byte-permute sign replication on the packed fp16 pairs.  The priors, the BC table gather and the
+// likelihood run on the CUDA cores of the same thread.
 //
-// Weights: the 5 hidden layers x {forward, transposed} x {hi, lo} fp16 images (640 KB) do not fit in shared
-// memory, so a loader warp streams the 64 KB image of the current step from L2 with bulk async copies into a
-// 2-deep ring; each image is used by the TWO tiles a CTA keeps in flight (one warpgroup each), so that the
-// MMAs of one tile overlap the epilogue of the other.
+// Weights: the 5 hidden layers x {forward, transposed} x {hi, lo} fp16 images (+ bias tiles, 680 KB) do not
+// fit in shared memory, so a loader warp streams the 68 KB image of the current stage from L2 with bulk async
+// copies into a 2-deep ring; each image is used by the TWO tiles a CTA keeps in flight (one warpgroup each),
+// so that the MMAs of one tile overlap the epilogue of the other.  The images of the four narrow stages
+// (28.5 KB) stay resident in shared memory.
 //
 // Warp roles (320 threads): warps 0-3 epilogue of tile A, warps 4-7 epilogue of tile B, warp 8 MMA issuer
 // (one elected lane) + TMEM allocator, warp 9 weight loader.
@@ -39,69 +49,196 @@ namespace tc {
 
 constexpr int kTile = 128;
 constexpr int kHid = 128;
-constexpr int kSteps = 10;                      // 5 forward + 5 transposed hidden layers
+constexpr int kStages = 14;                     // MMA stages per evaluation of a tile (7 in predict mode)
+constexpr int kRingImages = 10;                 // 5 forward + 5 transposed hidden layers
 constexpr uint32_t kImgBytes = 32768;           // one fp16 128x128 operand image
-constexpr uint32_t kStepBytes = 2 * kImgBytes;  // hi + lo
+constexpr uint32_t kBiasBytes = 4096;           // one fp16 128 (N) x 16 (K) bias tile
+constexpr uint32_t kStepBytes = 2 * kImgBytes + kBiasBytes;  // hi + lo + bias tile
 constexpr uint32_t kKStepBytes = 4096;          // 128 (N) x 16 (K) fp16
+constexpr uint32_t kKStep16 = 512;              // 16 (N) x 16 (K) fp16
 constexpr uint32_t kLbo = 128, kSbo = 256;
 constexpr int kThreads = 320;
 constexpr uint32_t kTmemCols = 512;
+constexpr int kGridPtsMax = 512;                // BC table axes kept in shared memory when they fit
 constexpr float kActScale = 512.0f;             // 2^9: activations up to ~127 stay finite in fp16
 
+// resident images (bytes into the resident blob)
+constexpr uint32_t rB0 = 0;                     // layer 0:  N = 128, K = 32
+constexpr uint32_t rB6 = rB0 + 2 * kKStepBytes; // layer 6:  N = 16, K = 128, hi then lo
+constexpr uint32_t rB6Bias = rB6 + 2 * 8 * kKStep16;  // N = 16, K = 16
+constexpr uint32_t rB7 = rB6Bias + kKStep16;    // layer 6^T: N = 128, K = 16
+constexpr uint32_t rB13 = rB7 + kKStepBytes;    // layer 0^T: N = 16, K = 128, hi then lo
+constexpr uint32_t kResidentBytes = rB13 + 2 * 8 * kKStep16;
+
 // offsets (floats) into the small-parameter blob
-constexpr int oW0 = 0;                  // [5][128]
-constexpr int oW0t = oW0 + 5 * 128;     // [128][8]
-constexpr int oB = oW0t + 128 * 8;      // [6][128]
-constexpr int oW6 = oB + 6 * 128;       // [128][4]
-constexpr int oB6 = oW6 + 128 * 4;      // [4]
-constexpr int oInLoc = oB6 + 4;         // [8]
+constexpr int oInLoc = 0;               // [8]
 constexpr int oInScale = oInLoc + 8;    // [8]
 constexpr int oOutLoc = oInScale + 8;   // [4]
 constexpr int oOutScale = oOutLoc + 4;  // [4]
-constexpr int oW6Max = oOutScale + 4;   // [4] max_j |W6[j][c]|
-constexpr int kSmallFloats = oW6Max + 4;
+constexpr int oGain = oOutScale + 4;    // [8] s_w * (largest row L1 norm) of the B image of stages 7..12
+constexpr int oBiasA = oGain + 8;       // [1] constant A entry of the bias products (+3 pad)
+constexpr int kSmallFloats = oBiasA + 4;
 
 struct __align__(128) Smem {
-  uint8_t wring[2][kStepBytes];  // weight ring: [buf][hi image | lo image]
+  uint8_t wring[2][kStepBytes];  // weight ring: [buf][hi image | lo image | bias tile]
+  uint8_t resident[kResidentBytes];
+  uint8_t a_const[kBiasBytes];   // constant A tile of the bias MMA: columns k = 0..2 hold oBiasA, rest 0
   float small[kSmallFloats];
-  uint32_t mask[24][256];        // ReLU masks: [hidden layer * 4 + word][epilogue thread]
+  uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
+  float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
+  unsigned short grid_lut[4][kLutBins];
   uint64_t w_full[2], w_empty[2], a_ready[2], d_ready[2];
   uint32_t tmem_base;
   double red[10 * 6];
   HyperVals hv;
 };
 
-// byte offset of element (n, k) inside one operand image (no-swizzle K-major core-matrix layout)
+// byte offset of element (n, k) inside an operand image with 128 rows (no-swizzle K-major core matrices)
 __host__ __device__ constexpr uint32_t img_offset(int n, int k) {
   return (uint32_t)(k >> 4) * kKStepBytes + (uint32_t)(n >> 3) * kSbo + (uint32_t)((k >> 3) & 1) * kLbo +
          (uint32_t)(n & 7) * 16 + (uint32_t)(k & 7) * 2;
 }
+// same for an image with 16 rows
+__host__ __device__ constexpr uint32_t img_offset16(int n, int k) {
+  return (uint32_t)(k >> 4) * kKStep16 + (uint32_t)(n >> 3) * kSbo + (uint32_t)((k >> 3) & 1) * kLbo +
+         (uint32_t)(n & 7) * 16 + (uint32_t)(k & 7) * 2;
+}
 
-// fp32 -> (hi, lo) fp16 pair: hi = rn16(v), lo = rn16(v - hi) (v - hi is exact in fp32); round-to-nearest on
-// both halves keeps 23 significant bits and leaves the dropped lo*lo term without a preferred sign
+// fp32 -> (hi, lo) fp16 pair: hi = rn16(v), lo = rn16(v - hi); v - hi is formed exactly by the mixed-precision
+// FMA (fma.rn.f32.f16: hi * -1 + v, SASS FHFMA).  Round-to-nearest on both halves keeps 23 significant bits
+// and leaves the dropped lo*lo term without a preferred sign.
 __device__ __forceinline__ void split2(float v0, float v1, uint32_t &hi, uint32_t &lo) {
   __half2 hh = __floats2half2_rn(v0, v1);
-  float2 hf = __half22float2(hh);
-  __half2 ll = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
   hi = *reinterpret_cast<uint32_t *>(&hh);
+  float l0, l1;
+  asm("{\n\t.reg .f16 h0, h1, m;\n\tmov.b32 {h0, h1}, %2;\n\tmov.b16 m, 0xBC00;\n\t"
+      "fma.rn.f32.f16 %0, h0, m, %3;\n\tfma.rn.f32.f16 %1, h1, m, %4;\n\t}"
+      : "=f"(l0), "=f"(l1)
+      : "r"(hi), "f"(v0), "f"(v1));
+  __half2 ll = __floats2half2_rn(l0, l1);
   lo = *reinterpret_cast<uint32_t *>(&ll);
 }
 
-// write 32 consecutive K-elements (chunk c) of this thread's row into the A operand region
-__device__ __forceinline__ void store_a_chunk(uint32_t a_base, int c, const float (&v)[32]) {
+// byte permute with sign replication (selector nibbles with bit 3 set replicate the msb of the chosen byte)
+template <uint32_t kSel>
+__device__ __forceinline__ uint32_t prmt_sign(uint32_t a) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(0u), "n"(kSel));
+  return d;
+}
+
+// Element e = 4 s + q of a 32-element chunk is shifted into the sign word at step t = 8 q + s, i.e. ends at bit
+// 31 - 8 q - s: after `word << s` the four elements of group s sit on the four byte msbs, which is what the
+// sign-replicating byte permute of the VJP needs.  bit = 1 means pre-activation < 0 (unit inactive).
+__device__ __forceinline__ uint32_t sign_word(const uint32_t (&r)[32]) {
+  uint32_t bits = 0;
+#pragma unroll
+  for (int t = 0; t < 32; ++t) bits = __funnelshift_l(r[4 * (t & 7) + (t >> 3)], bits, 1);
+  return bits;
+}
+
+// forward chunk: D (scaled pre-activations) -> ReLU -> activation scale -> (hi, lo) -> A operand columns
+__device__ __forceinline__ void fwd_chunk(const uint32_t (&r)[32], float scale, uint32_t a_base, int c) {
   uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int q = 0; q < 16; ++q) split2(v[2 * q], v[2 * q + 1], hi[q], lo[q]);
+  for (int q = 0; q < 16; ++q) {
+    const float v0 = fmaxf(__uint_as_float(r[2 * q]), 0.0f) * scale;
+    const float v1 = fmaxf(__uint_as_float(r[2 * q + 1]), 0.0f) * scale;
+    split2(v0, v1, hi[q], lo[q]);
+  }
   ptx::tmem_st16(a_base + 16 * c, hi);
   ptx::tmem_st16(a_base + 64 + 16 * c, lo);
 }
 
-// PREDICT = forward only (5 steps): writes predict's means / parameters instead of gradients (csi_predict).
+// VJP chunk: D (cotangent before the ReLU mask) -> row scale -> (hi, lo) -> mask on the packed pairs -> A operand
+__device__ __forceinline__ void bwd_chunk(const uint32_t (&r)[32], float f, uint32_t signs, uint32_t a_base, int c) {
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int s = 0; s < 8; ++s) {
+    const uint32_t w = signs << s;
+    const uint32_t ma = prmt_sign<0xAABBu>(w);  // elements 4s (low half), 4s+1 (high half)
+    const uint32_t mb = prmt_sign<0x8899u>(w);  // elements 4s+2, 4s+3
+    uint32_t h0, l0, h1, l1;
+    split2(__uint_as_float(r[4 * s]) * f, __uint_as_float(r[4 * s + 1]) * f, h0, l0);
+    split2(__uint_as_float(r[4 * s + 2]) * f, __uint_as_float(r[4 * s + 3]) * f, h1, l1);
+    hi[2 * s] = h0 & ~ma; lo[2 * s] = l0 & ~ma;
+    hi[2 * s + 1] = h1 & ~mb; lo[2 * s + 1] = l1 & ~mb;
+  }
+  ptx::tmem_st16(a_base + 16 * c, hi);
+  ptx::tmem_st16(a_base + 64 + 16 * c, lo);
+}
+
+// power of two f with f * x in [2^9, 2^10) (1 when x is 0 / non-finite)
+__device__ __forceinline__ float pow2_scale(float x) {
+  float f = 1.0f;
+  if (x > 0.0f && x < 3.0e38f) {
+    int e = (int)((__float_as_uint(x) >> 23) & 0xffu) - 127;
+    e = max(-100, min(100, e));
+    f = __uint_as_float((uint32_t)(9 - e + 127) << 23);
+  }
+  return f;
+}
+
+// pack two fp16 bit patterns (low, high)
+__device__ __forceinline__ uint32_t pack16(uint32_t lo16, uint32_t hi16) { return (lo16 & 0xffffu) | (hi16 << 16); }
+
+// D chunks (4 x 32 columns) through a two-register-set pipeline: the tcgen05.ld of the next chunk is in flight
+// while the current one is processed.  f(r, c) consumes chunk c.
+template <class F>
+__device__ __forceinline__ void for_chunks(uint32_t d_base, F &&f, int ncc = 2) {
+  uint32_t r0[32], r1[32];
+  ptx::tmem_ld32(d_base, r0);
+  ptx::tmem_wait_ld_dep(r0);
+#pragma unroll 1
+  for (int cc = 0; cc < ncc; ++cc) {
+    ptx::tmem_ld32(d_base + 64 * cc + 32, r1);
+    f(r0, 2 * cc);
+    ptx::tmem_wait_ld_dep(r1);
+    if (cc == 0) ptx::tmem_ld32(d_base + 64, r0);
+    f(r1, 2 * cc + 1);
+    if (cc == 0) ptx::tmem_wait_ld_dep(r0);
+  }
+}
+
+// one contraction = A_lo*B_hi + A_hi*B_lo (+ bias) + A_hi*B_hi over 8 K-steps, issued by one thread
+__device__ __forceinline__ void issue_3pass(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi, uint32_t b_lo,
+                                            uint32_t kstep_bytes, uint32_t idesc, bool bias, uint64_t a_const_desc,
+                                            uint32_t b_bias) {
+  uint32_t accumulate = 0;
+#pragma unroll
+  for (int pass = 0; pass < 3; ++pass) {
+    const uint32_t a_sel = pass == 0 ? a_lo : a_hi;
+    const uint32_t b_sel = pass == 1 ? b_lo : b_hi;
+    if (pass == 2 && bias)  // D += c_A * (b_hi + b_lo + b_lolo), exact to ~33 bits
+      ptx::mma_f16_ss(d, a_const_desc, ptx::make_smem_desc(b_bias, kLbo, kSbo), idesc, 1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      ptx::mma_f16_ts(d, a_sel + 8u * (uint32_t)j, ptx::make_smem_desc(b_sel + (uint32_t)j * kstep_bytes, kLbo, kSbo),
+                      idesc, accumulate);
+      accumulate = 1;
+    }
+  }
+}
+
+// clock64 trace (CSI_TC_DEBUG & 8): recorder `who` of CTA 0 appends (tag, clock) pairs to its 1024-entry region
+struct Tracer {
+  long long *p;
+  int n;
+  __device__ __forceinline__ void rec(int tag) {
+    if (p != nullptr && n < 510) { p[2 * n] = tag; p[2 * n + 1] = clock64(); ++n; }
+  }
+};
+
+__device__ __forceinline__ bool ring_stage(int s) { return (s >= 1 && s <= 5) || (s >= 8 && s <= 12); }
+
+// PREDICT = forward only (stages 0..6): writes predict's means / parameters instead of gradients (csi_predict).
 template <int BC, bool PREDICT>
 __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_constant__ Launch L) {
-  constexpr int kNSteps = PREDICT ? 5 : kSteps;
+  constexpr int kNStages = PREDICT ? 7 : kStages;
+  constexpr int kNRing = PREDICT ? 5 : kRingImages;
   extern __shared__ unsigned char smem_raw[];
-  Smem &S = *reinterpret_cast<Smem *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // align inside the shared window (keeps the pointer provably in the shared address space: LDS/STS, not LD/ST)
+  Smem &S = *reinterpret_cast<Smem *>(smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u));
   const DevModel &m = L.model;
   const StarIO &io = L.io;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -113,11 +250,33 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 
   // ---- one-time setup ----------------------------------------------------------------------------
   for (int i = tid; i < kSmallFloats; i += kThreads) S.small[i] = __ldg(L.tc.small + i);
+  for (int i = tid; i < (int)(kResidentBytes / 16); i += kThreads)
+    reinterpret_cast<uint4 *>(S.resident)[i] = __ldg(reinterpret_cast<const uint4 *>(L.tc.resident) + i);
+  const uint32_t ca16 = (uint32_t)__half_as_ushort(__float2half_rn(__ldg(L.tc.small + oBiasA)));
+  if (tid < 128) {
+    // constant A tile of the bias MMA, K-major core-matrix layout: row tid, k = 0..2 -> c_A, k = 3..15 -> 0
+    uint4 *row = reinterpret_cast<uint4 *>(S.a_const + (tid >> 3) * kSbo + (tid & 7) * 16);
+    row[0] = make_uint4(ca16 | (ca16 << 16), ca16, 0u, 0u);
+    row[kLbo / 16] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  GridDev gl = L.grid;
+  if (BC == 1 && gl.shape[0] + gl.shape[1] + gl.shape[2] + gl.shape[3] <= kGridPtsMax) {
+    int off = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      for (int i = tid; i < gl.shape[d]; i += kThreads) S.grid_pts[off + i] = L.grid.pts[d][i];
+      for (int i = tid; i < kLutBins; i += kThreads) S.grid_lut[d][i] = L.grid.lut[d][i];
+      gl.pts[d] = S.grid_pts + off;
+      gl.lut[d] = S.grid_lut[d];
+      off += gl.shape[d];
+    }
+  }
+  ptx::fence_proxy_async_smem();  // generic-proxy writes above are read by tcgen05.mma (async proxy)
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(&S.w_full[b], 1);
-      ptx::mbar_init(&S.w_empty[b], 1);
-      ptx::mbar_init(&S.a_ready[b], 128);  // every epilogue thread of the tile arrives
+      ptx::mbar_init(&S.w_empty[b], 2);  // one commit per tile
+      ptx::mbar_init(&S.a_ready[b], 4);  // one elected lane per epilogue warp of the tile
       ptx::mbar_init(&S.d_ready[b], 1);
     }
     ptx::fence_barrier_init();
@@ -134,54 +293,79 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   HyperAcc acc{};
 
   if (warp == 9) {
-    // ===== weight loader: stream the 64 KB image of every step into the 2-deep ring ====================
+    // ===== weight loader: stream the images of the ring stages into the 2-deep ring =====================
     if (lane == 0) {
-      const long long total = my_pairs * kNSteps;
+      const long long total = my_pairs * kNRing;
       for (long long it = 0; it < total; ++it) {
         const int buf = (int)(it & 1);
-        const int step = (int)(it % kNSteps);
+        const int r = (int)(it % kNRing);
+        const uint32_t bytes = r < 5 ? kStepBytes : 2 * kImgBytes;  // only forward images carry a bias tile
         ptx::mbar_wait(&S.w_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
-        ptx::mbar_arrive_expect_tx(&S.w_full[buf], kStepBytes);
-        const uint8_t *src = L.tc.img + (size_t)step * kStepBytes;
+        if ((L.tc.debug & 1) && it >= 2) { ptx::mbar_arrive(&S.w_full[buf]); continue; }  // timing experiment
+        ptx::mbar_arrive_expect_tx(&S.w_full[buf], bytes);
+        const uint8_t *src = L.tc.img + (size_t)r * kStepBytes;
 #pragma unroll
         for (int q = 0; q < 4; ++q)
           ptx::bulk_g2s(&S.wring[buf][q * 16384], src + q * 16384, 16384, &S.w_full[buf]);
+        if (r < 5) ptx::bulk_g2s(&S.wring[buf][2 * kImgBytes], src + 2 * kImgBytes, kBiasBytes, &S.w_full[buf]);
       }
     }
     __syncwarp();
   } else if (warp == 8) {
     // ===== MMA issuer ===============================================================================
-    const uint32_t idesc = ptx::make_idesc_f16(128, 128);
-    const long long total = my_pairs * kNSteps;
-    for (long long it = 0; it < total; ++it) {
-      const int buf = (int)(it & 1);
-      ptx::mbar_wait(&S.w_full[buf], (uint32_t)((it >> 1) & 1));
-      const uint32_t w_hi = ptx::smem_u32(&S.wring[buf][0]);
-      const uint32_t w_lo = w_hi + kImgBytes;
+    const uint32_t idesc128 = ptx::make_idesc_f16(128, 128);
+    const uint32_t idesc16 = ptx::make_idesc_f16(128, 16);
+    const uint64_t a_const_desc = ptx::make_smem_desc(ptx::smem_u32(S.a_const), kLbo, kSbo);
+    const uint32_t res = ptx::smem_u32(S.resident);
+    // The two tiles are served independently: whichever tile has published its A operand (and, for a ring
+    // stage, whose weight image has landed) gets its MMAs issued, so a long CUDA-core stage of one tile (priors,
+    // likelihood, table gathers) never blocks the tensor work of the other.
+    Tracer tr{(L.tc.trace && blockIdx.x == 0 && lane == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
+    int s_t[2] = {0, 0};
+    long long p_t[2] = {0, 0}, sc_t[2] = {0, 0}, q_t[2] = {0, 0};
+    bool done[2] = {my_pairs == 0, my_pairs == 0};
+    while (!(done[0] && done[1])) {
+#pragma unroll
       for (int t = 0; t < 2; ++t) {
-        ptx::mbar_wait(&S.a_ready[t], (uint32_t)(it & 1));
+        if (done[t]) continue;
+        const int s = s_t[t];
+        const bool ring = ring_stage(s);
+        const int buf = (int)(q_t[t] & 1);
+        if (!ptx::mbar_test_wait(&S.a_ready[t], (uint32_t)(sc_t[t] & 1))) continue;
+        if (ring && !ptx::mbar_test_wait(&S.w_full[buf], (uint32_t)((q_t[t] >> 1) & 1))) continue;
         ptx::tc_fence_after();
+        tr.rec(1000 + 100 * t + s);
         if (lane == 0) {
+          const uint32_t w_hi = ptx::smem_u32(&S.wring[buf][0]);
           const uint32_t d_t = tmem + (uint32_t)t * 256u;
           const uint32_t a_hi = d_t + 128u, a_lo = d_t + 192u;
-          uint32_t accumulate = 0;
-#pragma unroll
-          for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t a_sel = pass == 0 ? a_lo : a_hi;
-            const uint32_t w_sel = pass == 1 ? w_lo : w_hi;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint64_t bdesc = ptx::make_smem_desc(w_sel + (uint32_t)j * kKStepBytes, kLbo, kSbo);
-              ptx::mma_f16_ts(d_t, a_sel + 8u * (uint32_t)j, bdesc, idesc, accumulate);
-              accumulate = 1;
-            }
+          if (ring) {
+            issue_3pass(d_t, a_hi, a_lo, w_hi, w_hi + kImgBytes, kKStepBytes, idesc128, s <= 5, a_const_desc,
+                        w_hi + 2 * kImgBytes);
+          } else if (s == 0) {
+            ptx::mma_f16_ts(d_t, a_hi, ptx::make_smem_desc(res + rB0, kLbo, kSbo), idesc128, 0);
+            ptx::mma_f16_ts(d_t, a_hi + 8u, ptx::make_smem_desc(res + rB0 + kKStepBytes, kLbo, kSbo), idesc128, 1);
+          } else if (s == 6) {
+            issue_3pass(d_t, a_hi, a_lo, res + rB6, res + rB6 + 8 * kKStep16, kKStep16, idesc16, true, a_const_desc,
+                        res + rB6Bias);
+          } else if (s == 7) {
+            ptx::mma_f16_ts(d_t, a_hi, ptx::make_smem_desc(res + rB7, kLbo, kSbo), idesc128, 0);
+          } else {
+            issue_3pass(d_t, a_hi, a_lo, res + rB13, res + rB13 + 8 * kKStep16, kKStep16, idesc16, false, a_const_desc,
+                        0u);
           }
           ptx::mma_commit(&S.d_ready[t]);
+          if (ring) ptx::mma_commit(&S.w_empty[buf]);  // the slot is free once BOTH tiles' MMAs have read it
         }
+        tr.rec(2000 + 100 * t + s);
         __syncwarp();
+        ++sc_t[t];
+        if (ring) ++q_t[t];
+        if (++s_t[t] == kNStages) {
+          s_t[t] = 0;
+          if (++p_t[t] == my_pairs) done[t] = true;
+        }
       }
-      if (lane == 0) ptx::mma_commit(&S.w_empty[buf]);
-      __syncwarp();
     }
   } else {
     // ===== epilogue warpgroups: one thread = one star ===================================================
@@ -193,109 +377,99 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     const float *sm = S.small;
     const float inv_fwd = 1.0f / (kActScale * L.tc.w_scale);
     const float inv_wscale = 1.0f / L.tc.w_scale;
+    uint32_t *mask = &S.mask[0][tid];  // sign word of chunk c of hidden layer h at mask[(h * 4 + c) * 256]
+    // hand the A operand to the MMA warp: all tcgen05.st of this warp done, then one elected arrive
+    auto publish_a = [&]() {
+      ptx::tmem_wait_st();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&S.a_ready[t]);
+    };
+    Tracer tr{nullptr, 0};
+    if (L.tc.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
+      tr.p = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
     long long it = 0;
     for (long long p = 0; p < my_pairs; ++p) {
       const long long pair = (long long)blockIdx.x + p * gridDim.x;
       const long long i = (pair * 2 + t) * kTile + row;
       const bool valid = i < n;
+      // pull the next pair's inputs of this warp's 32 stars towards L2 (two lanes cover the <= 2 lines per array)
+      {
+        const long long inext = i + 2LL * kTile * gridDim.x;
+        if ((lane == 0 || lane == 31) && inext < n) {
+#pragma unroll
+          for (int sl = 0; sl < kSlots; ++sl)
+            if (io.z[sl]) ptx::prefetch_l2(io.z[sl] + inext);
+          for (int j = 0; j < m.n_obs; ++j) {
+            ptx::prefetch_l2(io.obs[j] + inext);
+            if (io.diag[j]) ptx::prefetch_l2(io.diag[j] + inext);
+          }
+          if (io.mh_loc) {
+            ptx::prefetch_l2(io.mh_loc + inext); ptx::prefetch_l2(io.mh_scale + inext); ptx::prefetch_l2(io.mh_logz + inext);
+          }
+        }
+      }
       StarState st;
       float x[5];
-      if (valid) {
+      if (valid && (L.tc.debug & 2)) {
+        st = StarState{};
+        st.x[0] = 0.3f; st.x[1] = 1.1f; st.x[2] = 0.1f; st.x[3] = 0.27f; st.x[4] = 2.0f; st.tau = 1.0f; st.dist = 100.f;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) / sm[oInScale + k] * kActScale;
+      } else if (valid) {
         star_pre(m, hv, io, i, st, acc);
 #pragma unroll
-        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) / sm[oInScale + k];
+        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) / sm[oInScale + k] * kActScale;
       } else {
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = 0.0f;
       }
-      uint32_t *mask = &S.mask[0][tid];  // word w of hidden layer h at mask[(h * 4 + w) * 256]
-      // ---- layer 0 (5 -> 128) on the CUDA cores, ReLU, mask, split, A operand of step 0 ----------------
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        float v[32];
-        uint32_t bits = 0;
+      // ---- A operand of stage 0: [x_hi(5) | x_lo(5) | x_hi(5) | c_A c_A c_A | 0 ...], K = 32 -> 16 columns ----
+      {
+        uint32_t h01, l01, h23, l23, h4, l4;
+        split2(x[0], x[1], h01, l01);
+        split2(x[2], x[3], h23, l23);
+        split2(x[4], 0.0f, h4, l4);
+        uint32_t a0[16];
+        a0[0] = h01; a0[1] = h23; a0[2] = pack16(h4, l01); a0[3] = pack16(l01 >> 16, l23);
+        a0[4] = pack16(l23 >> 16, l4); a0[5] = h01; a0[6] = h23; a0[7] = pack16(h4, ca16);
+        a0[8] = ca16 | (ca16 << 16);
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const int j = 32 * c + 4 * q;
-          float4 a = *reinterpret_cast<const float4 *>(sm + oB + j);
-#pragma unroll
-          for (int k = 0; k < 5; ++k) {
-            const float4 w = *reinterpret_cast<const float4 *>(sm + oW0 + k * 128 + j);
-            a.x = fmaf(x[k], w.x, a.x); a.y = fmaf(x[k], w.y, a.y);
-            a.z = fmaf(x[k], w.z, a.z); a.w = fmaf(x[k], w.w, a.w);
-          }
-          v[4 * q] = a.x; v[4 * q + 1] = a.y; v[4 * q + 2] = a.z; v[4 * q + 3] = a.w;
-        }
-#pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const bool on = v[e] > 0.0f;
-          bits |= (on ? 1u : 0u) << e;
-          v[e] = on ? v[e] * kActScale : 0.0f;
-        }
-        mask[(0 * 4 + c) * 256] = bits;
-        store_a_chunk(a_base, c, v);
+        for (int q = 9; q < 16; ++q) a0[q] = 0u;
+        ptx::tmem_st16(a_base, a0);
       }
-      ptx::tmem_wait_st();
-      ptx::tc_fence_before();
-      ptx::mbar_arrive(&S.a_ready[t]);
+      publish_a();
 
-      float g_o[4] = {0.f, 0.f, 0.f, 0.f};
-      float un = 1.0f;  // cotangent un-scaling: true value = D * un
+      float un = 1.0f;    // cotangent un-scaling: true value = D * un
+      float amax = 0.0f;  // max |A operand| of the current VJP stage (after scaling)
 #pragma unroll 1
-      for (int step = 0; step < kNSteps; ++step, ++it) {
+      for (int s = 0; s < kNStages; ++s, ++it) {
+        tr.rec(100 + s);
         ptx::mbar_wait(&S.d_ready[t], (uint32_t)(it & 1));
         ptx::tc_fence_after();
-        if (step < 4) {
-          // ---- hidden layer step+1 pre-activations -> ReLU -> next A operand -----------------------------
-          const float *bias = sm + oB + (step + 1) * 128;
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld32(d_base + 32 * c, r);
-            ptx::tmem_wait_ld();
-            float v[32];
-            uint32_t bits = 0;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float z = fmaf(__uint_as_float(r[e]), inv_fwd, bias[32 * c + e]);
-              const bool on = z > 0.0f;
-              bits |= (on ? 1u : 0u) << e;
-              v[e] = on ? z * kActScale : 0.0f;
-            }
-            mask[((step + 1) * 4 + c) * 256] = bits;
-            store_a_chunk(a_base, c, v);
-          }
-        } else if (step == 4) {
-          // ---- last hidden layer -> output layer (128 -> 4) -> likelihood -> cotangent of hidden 5 --------
-          const float *bias = sm + oB + 5 * 128;
-          float y[4] = {sm[oB6], sm[oB6 + 1], sm[oB6 + 2], sm[oB6 + 3]};
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld32(d_base + 32 * c, r);
-            ptx::tmem_wait_ld();
-            uint32_t bits = 0;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float z = fmaf(__uint_as_float(r[e]), inv_fwd, bias[32 * c + e]);
-              const bool on = z > 0.0f;
-              bits |= (on ? 1u : 0u) << e;
-              const float a = on ? z : 0.0f;
-              const float4 w = *reinterpret_cast<const float4 *>(sm + oW6 + (32 * c + e) * 4);
-              y[0] = fmaf(a, w.x, y[0]); y[1] = fmaf(a, w.y, y[1]);
-              y[2] = fmaf(a, w.z, y[2]); y[3] = fmaf(a, w.w, y[3]);
-            }
-            mask[(5 * 4 + c) * 256] = bits;
-          }
+        tr.rec(200 + s);
+        if (s <= 5) {
+          // ---- pre-activations of hidden layer s (bias already in D) -> sign word, ReLU -> next A operand ----
+          uint32_t *mk = mask + s * 4 * 256;
+          for_chunks(d_base, [&](const uint32_t (&r)[32], int c) {
+            mk[c * 256] = sign_word(r);
+            fwd_chunk(r, inv_wscale, a_base, c);
+          }, (L.tc.debug & 4) ? 1 : 2);
+        } else if (s == 6) {
+          // ---- emulator outputs -> predict + likelihood -> cotangent of the outputs -> A operand of stage 7 ----
+          uint32_t r8[8];
+          ptx::tmem_ld8(d_base, r8);
+          ptx::tmem_wait_ld_dep8(r8);
           float g_y[4] = {0.f, 0.f, 0.f, 0.f};
           if (valid) {
-            float o[4];
+            float o[4], g_o[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) o[c] = sm[oOutLoc + c] + sm[oOutScale + c] * y[c];
+            for (int c = 0; c < 4; ++c) o[c] = sm[oOutLoc + c] + sm[oOutScale + c] * (__uint_as_float(r8[c]) * inv_fwd);
             float mean_local[kMaxMean];
             float *mo = PREDICT ? mean_local : nullptr;
-            if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, mo); }
-            if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc, mo); }
+            if (L.tc.debug & 2) { g_o[0] = o[0]; g_o[1] = o[1]; g_o[2] = o[2]; g_o[3] = o[3]; }
+            else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, mo); }
+            else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, mo); }
 #pragma unroll
             for (int c = 0; c < 4; ++c) g_y[c] = g_o[c] * sm[oOutScale + c];
             if (PREDICT) {
@@ -304,96 +478,57 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
                 for (int k = 0; k < kMaxMean; ++k) L.mean_out[i * kMaxMean + k] = mean_local[k];
               }
               if (L.params_out) {
-                float4 *p = reinterpret_cast<float4 *>(L.params_out + i * 8);
-                p[0] = make_float4(st.x[0], st.x[1], st.x[2], st.x[3]);
-                p[1] = make_float4(st.x[4], st.log_mass, st.tau, st.dist);
+                float4 *pp = reinterpret_cast<float4 *>(L.params_out + i * 8);
+                pp[0] = make_float4(st.x[0], st.x[1], st.x[2], st.x[3]);
+                pp[1] = make_float4(st.x[4], st.log_mass, st.tau, st.dist);
               }
             }
           }
           if (!PREDICT) {
-          // per-row power-of-two scale from a bound on |g_y W6^T|
-          float bound = fabsf(g_y[0]) * sm[oW6Max] + fabsf(g_y[1]) * sm[oW6Max + 1] + fabsf(g_y[2]) * sm[oW6Max + 2] +
-                        fabsf(g_y[3]) * sm[oW6Max + 3];
-          float f = 1.0f;
-          if (bound > 0.0f && bound < 3.0e38f) {
-            int e = (int)((__float_as_uint(bound) >> 23) & 0xffu) - 127;
-            e = max(-100, min(100, e));
-            f = __uint_as_float((uint32_t)(9 - e + 127) << 23);
+            // [g_hi(4) | g_lo(4) | g_hi(4) | 0(4)] with a per-row power-of-two scale, K = 16 -> 8 columns
+            const float gmax = fmaxf(fmaxf(fabsf(g_y[0]), fabsf(g_y[1])), fmaxf(fabsf(g_y[2]), fabsf(g_y[3])));
+            const float f = pow2_scale(gmax);
+            un = 1.0f / f * inv_wscale;  // after the MMA: D = sum (g f)(w s_w)  ->  g_in = D / (f s_w)
+            amax = gmax * f;
+            uint32_t h01, l01, h23, l23;
+            split2(g_y[0] * f, g_y[1] * f, h01, l01);
+            split2(g_y[2] * f, g_y[3] * f, h23, l23);
+            const uint32_t ag[8] = {h01, h23, l01, l23, h01, h23, 0u, 0u};
+            ptx::tmem_st8(a_base, ag);
           }
-          un = 1.0f / f * inv_wscale;  // after the MMA: D = sum (g f)(w s_w)  ->  g_in = D / (f s_w)
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            float v[32];
-            const uint32_t bits = mask[(5 * 4 + c) * 256];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float4 w = *reinterpret_cast<const float4 *>(sm + oW6 + (32 * c + e) * 4);
-              const float g = (g_y[0] * w.x + g_y[1] * w.y + g_y[2] * w.z + g_y[3] * w.w) * f;
-              v[e] = ((bits >> e) & 1u) ? g : 0.0f;
-            }
-            store_a_chunk(a_base, c, v);
-          }
-          }  // !PREDICT
-        } else if (step < 9) {
-          // ---- cotangent of hidden layer h = 9 - step: ReLU mask, re-scale, next A operand ----------------
-          const int h = 9 - step;
+        } else if (s <= 12) {
+          // ---- cotangent of hidden layer h = 12 - s: re-scale, ReLU mask, next A operand --------------------
+          // |D| <= amax * (s_w * G) with G = the largest row L1 norm of this stage's B image, so the scale is
+          // known BEFORE D is read (one pass); the exact row maximum is gathered for the next stage.
+          const int h = 12 - s;
+          const float f = pow2_scale(amax * sm[oGain + (s - 7)]) * 32.0f;  // f * |D| < 2^15
           float mx = 0.0f;
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld32(d_base + 32 * c, r);
-            ptx::tmem_wait_ld();
+          const uint32_t *mk = mask + h * 4 * 256;
+          for_chunks(d_base, [&](const uint32_t (&r)[32], int c) {
 #pragma unroll
-            for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fabsf(__uint_as_float(r[e])));
-          }
-          float f = 1.0f;
-          if (mx > 0.0f && mx < 3.0e38f) {
-            int e = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 127;
-            e = max(-100, min(100, e));
-            f = __uint_as_float((uint32_t)(9 - e + 127) << 23);
-          }
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld32(d_base + 32 * c, r);
-            ptx::tmem_wait_ld();
-            float v[32];
-            const uint32_t bits = mask[(h * 4 + c) * 256];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) v[e] = ((bits >> e) & 1u) ? __uint_as_float(r[e]) * f : 0.0f;
-            store_a_chunk(a_base, c, v);
-          }
+            for (int e = 0; e < 32; e += 2)
+              mx = fmaxf(mx, fmaxf(fabsf(__uint_as_float(r[e])), fabsf(__uint_as_float(r[e + 1]))));
+            bwd_chunk(r, f, mk[c * 256], a_base, c);
+          }, (L.tc.debug & 4) ? 1 : 2);
+          amax = mx * f;
           un = un / f * inv_wscale;
         } else {
-          // ---- cotangent of hidden layer 0 -> layer-0 VJP (128 -> 5) -> gradient stores -----------------
-          float gh[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-          for (int c = 0; c < 4; ++c) {
-            uint32_t r[32];
-            ptx::tmem_ld32(d_base + 32 * c, r);
-            ptx::tmem_wait_ld();
-            const uint32_t bits = mask[(0 * 4 + c) * 256];
-#pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const float g = ((bits >> e) & 1u) ? __uint_as_float(r[e]) : 0.0f;
-              const float4 w0 = *reinterpret_cast<const float4 *>(sm + oW0t + (32 * c + e) * 8);
-              const float w4 = sm[oW0t + (32 * c + e) * 8 + 4];
-              gh[0] = fmaf(g, w0.x, gh[0]); gh[1] = fmaf(g, w0.y, gh[1]); gh[2] = fmaf(g, w0.z, gh[2]);
-              gh[3] = fmaf(g, w0.w, gh[3]); gh[4] = fmaf(g, w4, gh[4]);
-            }
-          }
+          // ---- cotangent of the (normalised) emulator inputs -> chain rule to the sites -> gradient stores ------
+          uint32_t r8[8];
+          ptx::tmem_ld8(d_base, r8);
+          ptx::tmem_wait_ld_dep8(r8);
           if (valid) {
             float g_x[5];
 #pragma unroll
-            for (int k = 0; k < 5; ++k) g_x[k] = gh[k] * un / sm[oInScale + k];
+            for (int k = 0; k < 5; ++k) g_x[k] = __uint_as_float(r8[k]) * un / sm[oInScale + k];
             star_post(m, io, i, st, g_x);
             acc.lp += (double)st.lp;
           }
         }
-        if (step < kNSteps - 1) {
-          ptx::tmem_wait_st();
-          ptx::tc_fence_before();
-          ptx::mbar_arrive(&S.a_ready[t]);
+        tr.rec(300 + s);
+        if (s < kNStages - 1) {
+          publish_a();
+          tr.rec(400 + s);
         } else {
           // all reads of D are complete (wait::ld above); order them before the next pair's MMAs
           ptx::tc_fence_before();
@@ -414,63 +549,133 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 // -----------------------------------------------------------------------------------------------------
 // host side
 // -----------------------------------------------------------------------------------------------------
-bool tc_supported(const csi_net &net) {
-  return net.n_layers == 7 && net.n_in == 5 && net.n_hidden == 128 && net.n_out == 4;
-}
-size_t tc_image_bytes(const csi_net &) { return (size_t)tc::kSteps * tc::kStepBytes; }
-size_t tc_small_floats(const csi_net &) { return tc::kSmallFloats; }
-
 static uint16_t half_bits(float v) {
   __half h = __float2half_rn(v);
   uint16_t b;
   std::memcpy(&b, &h, 2);
   return b;
 }
+static float half_value(uint16_t b) {
+  __half h;
+  std::memcpy(static_cast<void *>(&h), &b, 2);
+  return __half2float(h);
+}
+static void put16(uint8_t *base, uint32_t off, uint16_t v) { std::memcpy(base + off, &v, 2); }
+// (hi, lo) fp16 split of a host value, round-to-nearest on both halves
+static void split_host(float v, uint16_t *hi, uint16_t *lo) {
+  *hi = half_bits(v);
+  *lo = half_bits(v - half_value(*hi));
+}
 
-void tc_build_images(const csi_net &net, uint8_t *img, float *small, float *act_scale, float *w_scale) {
-  using namespace tc;
-  // weight scale: largest power of two with max|W| * s <= 32768 over the hidden layers
-  float wmax = 0.f;
-  for (int l = 1; l <= 5; ++l)
-    for (int i = 0; i < kHid * kHid; ++i) wmax = std::fmax(wmax, std::fabs(net.weights[l][i]));
+// operand scalings: weights by s_w = the largest power of two with max|W| s_w <= 32768 (all layers); the bias
+// products use a constant A entry c_A = the smallest power of two with act_scale * s_w * max|b| / c_A <= 32768
+static void tc_scales(const csi_net &net, float *w_scale, float *bias_a) {
+  float wmax = 0.f, bmax = 0.f;
+  for (int l = 0; l < 7; ++l) {
+    const int K = l == 0 ? 5 : tc::kHid, N = l == 6 ? 4 : tc::kHid;
+    for (int i = 0; i < K * N; ++i) wmax = std::fmax(wmax, std::fabs(net.weights[l][i]));
+    for (int i = 0; i < N; ++i) bmax = std::fmax(bmax, std::fabs(net.bias[l][i]));
+  }
   float s = 1.0f;
   if (wmax > 0.f) s = std::exp2(std::floor(std::log2(32768.0f / wmax)));
+  float ca = 1.0f;
+  const float need = tc::kActScale * s * bmax / 32768.0f;
+  if (need > 1.0f) ca = std::exp2(std::ceil(std::log2(need)));
+  *w_scale = s;
+  *bias_a = ca;
+}
+
+bool tc_supported(const csi_net &net) {
+  if (!(net.n_layers == 7 && net.n_in == 5 && net.n_hidden == 128 && net.n_out == 4)) return false;
+  float s, ca;
+  tc_scales(net, &s, &ca);
+  return std::isfinite(s) && ca <= 32768.0f;  // the bias tile must fit the fp16 range
+}
+size_t tc_image_bytes(const csi_net &) { return (size_t)tc::kRingImages * tc::kStepBytes; }
+size_t tc_resident_bytes(const csi_net &) { return tc::kResidentBytes; }
+size_t tc_small_floats(const csi_net &) { return tc::kSmallFloats; }
+
+void tc_build_images(const csi_net &net, uint8_t *img, uint8_t *res, float *small, float *act_scale, float *w_scale) {
+  using namespace tc;
+  float s, ca;
+  tc_scales(net, &s, &ca);
   *w_scale = s;
   *act_scale = kActScale;
-  std::memset(img, 0, (size_t)kSteps * kStepBytes);
-  for (int step = 0; step < kSteps; ++step) {
-    const bool fwd = step < 5;
-    const int l = fwd ? step + 1 : 10 - step;  // bwd: layers 5,4,3,2,1
-    const float *W = net.weights[l];           // [in][out]
-    uint8_t *hi = img + (size_t)step * kStepBytes, *lo = hi + kImgBytes;
-    for (int nn = 0; nn < kHid; ++nn)
+  const float bias_mul = kActScale * s / ca;
+  const double slack = 1.0 + 1.0 / 256.0;  // covers the rounding of the split operands in the a-priori bounds
+  std::memset(img, 0, (size_t)kRingImages * kStepBytes);
+  std::memset(res, 0, kResidentBytes);
+  std::memset(small, 0, sizeof(float) * kSmallFloats);
+  auto put_bias = [&](uint8_t *tile, uint32_t off0, uint32_t off1, uint32_t off2, float b) {
+    const uint16_t b0 = half_bits(b);
+    const float r1 = b - half_value(b0);
+    const uint16_t b1 = half_bits(r1);
+    const uint16_t b2 = half_bits(r1 - half_value(b1));
+    put16(tile, off0, b0); put16(tile, off1, b1); put16(tile, off2, b2);
+  };
+  // ---- streamed images: forward layers 1..5, then transposed layers 5..1 ----------------------------------
+  for (int r = 0; r < kRingImages; ++r) {
+    const bool fwd = r < 5;
+    const int l = fwd ? r + 1 : 10 - r;
+    const float *W = net.weights[l];  // [in][out]
+    uint8_t *hi = img + (size_t)r * kStepBytes, *lo = hi + kImgBytes, *bt = lo + kImgBytes;
+    double gain = 0.0;
+    for (int nn = 0; nn < kHid; ++nn) {
+      double l1 = 0.0;
       for (int k = 0; k < kHid; ++k) {
         // forward: B[n = out][k = in] = W[k][n];  transposed: B[n = in][k = out] = W[n][k]
         const float w = (fwd ? W[(size_t)k * kHid + nn] : W[(size_t)nn * kHid + k]) * s;
-        const uint16_t hb = half_bits(w);
-        __half hh;
-        std::memcpy(&hh, &hb, 2);
-        const uint16_t lb = half_bits(w - __half2float(hh));
-        const uint32_t off = img_offset(nn, k);
-        std::memcpy(hi + off, &hb, 2);
-        std::memcpy(lo + off, &lb, 2);
+        uint16_t hb, lb;
+        split_host(w, &hb, &lb);
+        put16(hi, img_offset(nn, k), hb);
+        put16(lo, img_offset(nn, k), lb);
+        l1 += std::fabs((double)w);
       }
+      gain = std::fmax(gain, l1);
+      if (fwd) put_bias(bt, img_offset(nn, 0), img_offset(nn, 1), img_offset(nn, 2), net.bias[l][nn] * bias_mul);
+    }
+    if (!fwd) small[oGain + 1 + (r - 5)] = (float)(gain * slack);  // stages 8..12
   }
-  std::memset(small, 0, sizeof(float) * kSmallFloats);
-  for (int k = 0; k < 5; ++k)
-    for (int j = 0; j < 128; ++j) {
-      small[oW0 + k * 128 + j] = net.weights[0][k * 128 + j];
-      small[oW0t + j * 8 + k] = net.weights[0][k * 128 + j];
+  // ---- stage 0: layer 0, K = 32: [W0_hi (5) | W0_hi (5) | W0_lo (5) | bias split (3) | 0] per output unit ----
+  for (int j = 0; j < kHid; ++j) {
+    for (int k = 0; k < 5; ++k) {
+      uint16_t hb, lb;
+      split_host(net.weights[0][k * kHid + j] * s, &hb, &lb);
+      put16(res + rB0, img_offset(j, k), hb);
+      put16(res + rB0, img_offset(j, 5 + k), hb);
+      put16(res + rB0, img_offset(j, 10 + k), lb);
     }
-  for (int l = 0; l < 6; ++l)
-    for (int j = 0; j < 128; ++j) small[oB + l * 128 + j] = net.bias[l][j];
-  for (int j = 0; j < 128; ++j)
+    put_bias(res + rB0, img_offset(j, 15), img_offset(j, 16), img_offset(j, 17), net.bias[0][j] * bias_mul);
+  }
+  // ---- stage 6: layer 6, N = 16 (4 used), K = 128, + bias tile; stage 7: its transpose, K = 16 -----------------
+  double gain7 = 0.0;
+  for (int j = 0; j < kHid; ++j) {
+    double l1 = 0.0;
     for (int c = 0; c < 4; ++c) {
-      small[oW6 + j * 4 + c] = net.weights[6][j * 4 + c];
-      small[oW6Max + c] = std::fmax(small[oW6Max + c], std::fabs(net.weights[6][j * 4 + c]));
+      uint16_t hb, lb;
+      split_host(net.weights[6][j * 4 + c] * s, &hb, &lb);
+      put16(res + rB6, img_offset16(c, j), hb);
+      put16(res + rB6 + 8 * kKStep16, img_offset16(c, j), lb);
+      put16(res + rB7, img_offset(j, c), hb);
+      put16(res + rB7, img_offset(j, 4 + c), hb);
+      put16(res + rB7, img_offset(j, 8 + c), lb);
+      l1 += std::fabs((double)net.weights[6][j * 4 + c] * s);
     }
+    gain7 = std::fmax(gain7, l1);
+  }
+  small[oGain + 0] = (float)(gain7 * slack);  // stage 7
+  for (int c = 0; c < 4; ++c)
+    put_bias(res + rB6Bias, img_offset16(c, 0), img_offset16(c, 1), img_offset16(c, 2), net.bias[6][c] * bias_mul);
+  // ---- stage 13: layer 0 transposed, N = 16 (5 used), K = 128 ---------------------------------------------
+  for (int k = 0; k < 5; ++k)
+    for (int j = 0; j < kHid; ++j) {
+      uint16_t hb, lb;
+      split_host(net.weights[0][k * kHid + j] * s, &hb, &lb);
+      put16(res + rB13, img_offset16(k, j), hb);
+      put16(res + rB13 + 8 * kKStep16, img_offset16(k, j), lb);
+    }
+  small[oBiasA] = ca;
   for (int c = 0; c < 4; ++c) {
-    small[oB6 + c] = net.bias[6][c];
     small[oOutLoc + c] = (float)net.out_loc[c];
     small[oOutScale + c] = (float)net.out_scale[c];
   }

@@ -1,0 +1,157 @@
+// csi_ubench.cu -- micro-benchmarks of the tcgen05 building blocks on one SM (cycle counts via clock64):
+//   MMA throughput for the shapes the engine uses (A from TMEM, B from smem), dependent vs independent
+//   accumulators, commit -> mbarrier wake-up latency, tcgen05.ld / tcgen05.st round trips.
+// usage: csi_ubench            (prints one line per measurement)
+#include <cuda_fp16.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "csi_ptx.cuh"
+
+using namespace csi;
+
+struct __align__(128) USmem {
+  uint8_t b_img[65536];
+  uint64_t bar, bar2;
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(160) ubench_kernel(long long *out) {
+  extern __shared__ unsigned char raw[];
+  USmem &S = *reinterpret_cast<USmem *>(raw + ((1024u - (ptx::smem_u32(raw) & 1023u)) & 1023u));
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 65536 / 16; i += blockDim.x) reinterpret_cast<uint4 *>(S.b_img)[i] = make_uint4(0, 0, 0, 0);
+  ptx::fence_proxy_async_smem();
+  if (tid == 0) { ptx::mbar_init(&S.bar, 1); ptx::mbar_init(&S.bar2, 1); ptx::fence_barrier_init(); }
+  if (warp == 4) ptx::tmem_alloc<512>(&S.tmem_base);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = S.tmem_base;
+  const uint32_t b_s = ptx::smem_u32(S.b_img);
+  uint32_t par = 0;
+  // ---- MMA throughput: n_mma MMAs of (N, one or two accumulators), issued by one thread -------------------
+  const int shapesN[3] = {128, 64, 16};
+  for (int sh = 0; sh < 3; ++sh)
+    for (int two = 0; two < 2; ++two) {
+      const int N = shapesN[sh];
+      const uint32_t idesc = ptx::make_idesc_f16(128, N);
+      const int n_mma = 200;
+      __syncthreads();
+      if (tid == 128) {
+        long long t0 = clock64();
+        for (int j = 0; j < n_mma; ++j) {
+          const uint32_t d = tmem + ((two && (j & 1)) ? 256u : 0u);
+          ptx::mma_f16_ts(d, tmem + 128u + 8u * (j & 7), ptx::make_smem_desc(b_s + (j & 7) * 4096, 128, 256), idesc, j > 1);
+        }
+        long long t1 = clock64();
+        ptx::mma_commit(&S.bar);
+        ptx::mbar_wait(&S.bar, par);
+        long long t2 = clock64();
+        out[(sh * 2 + two) * 2] = t1 - t0;
+        out[(sh * 2 + two) * 2 + 1] = t2 - t0;
+      }
+      par ^= 1;
+      __syncthreads();
+    }
+  // ---- SS-mode (A from smem) N = 128 ------------------------------------------------------------------
+  {
+    const uint32_t idesc = ptx::make_idesc_f16(128, 128);
+    __syncthreads();
+    if (tid == 128) {
+      long long t0 = clock64();
+      for (int j = 0; j < 200; ++j)
+        ptx::mma_f16_ss(tmem, ptx::make_smem_desc(b_s + 32768 + (j & 7) * 4096, 128, 256),
+                        ptx::make_smem_desc(b_s + (j & 7) * 4096, 128, 256), idesc, j > 0);
+      ptx::mma_commit(&S.bar);
+      ptx::mbar_wait(&S.bar, par);
+      out[12] = clock64() - t0;
+    }
+    par ^= 1;
+    __syncthreads();
+  }
+  // ---- hand-off latency: 1 MMA + commit -> waiter on another warp sees it ---------------------------------
+  {
+    const uint32_t idesc = ptx::make_idesc_f16(128, 128);
+    __shared__ long long t_issue, t_seen;
+    __syncthreads();
+    if (tid == 128) {
+      t_issue = clock64();
+      ptx::mma_f16_ts(tmem, tmem + 128u, ptx::make_smem_desc(b_s, 128, 256), idesc, 0);
+      ptx::mma_commit(&S.bar2);
+    }
+    if (warp == 0) {
+      ptx::mbar_wait(&S.bar2, 0);
+      if (lane == 0) t_seen = clock64();
+    }
+    __syncthreads();
+    if (tid == 0) out[13] = t_seen - t_issue;
+  }
+  // ---- tcgen05.ld x32 + wait, and st x16 x2 + wait::st, one warp alone and four warps together --------------
+  for (int four = 0; four < 2; ++four) {
+    __syncthreads();
+    if (warp < (four ? 4 : 1)) {
+      const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+      uint32_t r[32];
+      long long t0 = clock64();
+      for (int it = 0; it < 16; ++it) {
+        ptx::tmem_ld32(tmem + lane_base + 32 * (it & 3), r);
+        ptx::tmem_wait_ld_dep(r);
+      }
+      long long t1 = clock64();
+      uint32_t h[16];
+#pragma unroll
+      for (int q = 0; q < 16; ++q) h[q] = r[q] + r[q + 16];
+      for (int it = 0; it < 16; ++it) {
+        ptx::tmem_st16(tmem + lane_base + 128 + 16 * (it & 3), h);
+        ptx::tmem_st16(tmem + lane_base + 192 + 16 * (it & 3), h);
+        ptx::tmem_wait_st();
+      }
+      long long t2 = clock64();
+      // back-to-back loads without waiting in between (throughput)
+      uint32_t r2[32];
+      for (int it = 0; it < 8; ++it) {
+        ptx::tmem_ld32(tmem + lane_base + 32 * (it & 3), r);
+        ptx::tmem_ld32(tmem + lane_base + 32 * ((it + 1) & 3), r2);
+        ptx::tmem_wait_ld_dep(r);
+        ptx::tmem_wait_ld_dep(r2);
+      }
+      long long t3 = clock64();
+      if (lane == 0 && warp == 0) {
+        out[14 + four * 3] = (t1 - t0) / 16;
+        out[15 + four * 3] = (t2 - t1) / 16;
+        out[16 + four * 3] = (t3 - t2) / 16;
+      }
+      if (r[0] + r2[1] == 0x12345678u) out[30] = 1;
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) ptx::tmem_dealloc<512>(tmem);
+}
+
+int main() {
+  long long *d, h[32] = {0};
+  cudaMalloc(&d, sizeof(h));
+  cudaMemset(d, 0, sizeof(h));
+  const int smem = (int)sizeof(USmem) + 1024;
+  cudaFuncSetAttribute(ubench_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  for (int rep = 0; rep < 2; ++rep) {
+    ubench_kernel<<<1, 160, smem>>>(d);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { printf("CUDA error %s\n", cudaGetErrorString(e)); return 1; }
+  }
+  cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  const char *names[3] = {"N=128", "N=64", "N=16"};
+  for (int sh = 0; sh < 3; ++sh)
+    for (int two = 0; two < 2; ++two)
+      printf("mma TS M=128 %s K=16 x200, %s accumulator(s): issue %lld cyc total, complete %lld cyc total = %.1f cyc/MMA\n",
+             names[sh], two ? "two alternating" : "one", h[(sh * 2 + two) * 2], h[(sh * 2 + two) * 2 + 1],
+             h[(sh * 2 + two) * 2 + 1] / 200.0);
+  printf("mma SS M=128 N=128 x200: %.1f cyc/MMA\n", h[12] / 200.0);
+  printf("1 MMA + commit -> waiting warp resumes: %lld cyc\n", h[13]);
+  for (int four = 0; four < 2; ++four)
+    printf("%s: tcgen05.ld x32 + wait %lld cyc, 2 x tcgen05.st x16 + wait %lld cyc, 2 x ld x32 back to back %lld cyc\n",
+           four ? "4 warps" : "1 warp ", h[14 + four * 3], h[15 + four * 3], h[16 + four * 3]);
+  return 0;
+}
