@@ -87,43 +87,45 @@ __global__ void __launch_bounds__(160) ubench_kernel(long long *out) {
     __syncthreads();
     if (tid == 0) out[13] = t_seen - t_issue;
   }
-  // ---- tcgen05.ld x32 + wait, and st x16 x2 + wait::st, one warp alone and four warps together --------------
-  for (int four = 0; four < 2; ++four) {
+  // ---- tcgen05.ld x32 + wait (dependent use), idle tensor pipe vs MMAs streaming from another warp -------------
+  for (int busy = 0; busy < 2; ++busy) {
     __syncthreads();
-    if (warp < (four ? 4 : 1)) {
+    if (tid == 128 && busy) {
+      const uint32_t idesc = ptx::make_idesc_f16(128, 128);
+      for (int j = 0; j < 120; ++j)
+        ptx::mma_f16_ts(tmem + 256u, tmem + 384u + 8u * (j & 7), ptx::make_smem_desc(b_s + (j & 7) * 4096, 128, 256), idesc, j > 0);
+      ptx::mma_commit(&S.bar);
+    }
+    if (warp < 4) {
       const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
-      uint32_t r[32];
+      uint32_t r[32], acc = 0;
+      if (busy) __nanosleep(1000);
       long long t0 = clock64();
-      for (int it = 0; it < 16; ++it) {
+      for (int it = 0; it < 8; ++it) {
         ptx::tmem_ld32(tmem + lane_base + 32 * (it & 3), r);
         ptx::tmem_wait_ld_dep(r);
+#pragma unroll
+        for (int q = 0; q < 32; ++q) acc += r[q];
+        asm volatile("" ::"r"(acc) : "memory");
       }
       long long t1 = clock64();
       uint32_t h[16];
 #pragma unroll
-      for (int q = 0; q < 16; ++q) h[q] = r[q] + r[q + 16];
-      for (int it = 0; it < 16; ++it) {
+      for (int q = 0; q < 16; ++q) h[q] = acc + q;
+      for (int it = 0; it < 8; ++it) {
         ptx::tmem_st16(tmem + lane_base + 128 + 16 * (it & 3), h);
         ptx::tmem_st16(tmem + lane_base + 192 + 16 * (it & 3), h);
         ptx::tmem_wait_st();
       }
       long long t2 = clock64();
-      // back-to-back loads without waiting in between (throughput)
-      uint32_t r2[32];
-      for (int it = 0; it < 8; ++it) {
-        ptx::tmem_ld32(tmem + lane_base + 32 * (it & 3), r);
-        ptx::tmem_ld32(tmem + lane_base + 32 * ((it + 1) & 3), r2);
-        ptx::tmem_wait_ld_dep(r);
-        ptx::tmem_wait_ld_dep(r2);
-      }
-      long long t3 = clock64();
       if (lane == 0 && warp == 0) {
-        out[14 + four * 3] = (t1 - t0) / 16;
-        out[15 + four * 3] = (t2 - t1) / 16;
-        out[16 + four * 3] = (t3 - t2) / 16;
+        out[14 + busy * 3] = (t1 - t0) / 8;
+        out[15 + busy * 3] = (t2 - t1) / 8;
+        out[16 + busy * 3] = acc;
       }
-      if (r[0] + r2[1] == 0x12345678u) out[30] = 1;
     }
+    if (tid == 128 && busy) { ptx::mbar_wait(&S.bar, par); par ^= 1; }
+    __syncthreads();
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -150,8 +152,8 @@ int main() {
              h[(sh * 2 + two) * 2 + 1] / 200.0);
   printf("mma SS M=128 N=128 x200: %.1f cyc/MMA\n", h[12] / 200.0);
   printf("1 MMA + commit -> waiting warp resumes: %lld cyc\n", h[13]);
-  for (int four = 0; four < 2; ++four)
-    printf("%s: tcgen05.ld x32 + wait %lld cyc, 2 x tcgen05.st x16 + wait %lld cyc, 2 x ld x32 back to back %lld cyc\n",
-           four ? "4 warps" : "1 warp ", h[14 + four * 3], h[15 + four * 3], h[16 + four * 3]);
+  for (int busy = 0; busy < 2; ++busy)
+    printf("4 warps, tensor pipe %s: tcgen05.ld x32 + wait + use %lld cyc, 2 x tcgen05.st x16 + wait %lld cyc\n",
+           busy ? "busy (MMA N=128 stream)" : "idle", h[14 + busy * 3], h[15 + busy * 3]);
   return 0;
 }
