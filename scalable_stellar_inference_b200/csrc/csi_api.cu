@@ -447,6 +447,8 @@ static void fill_launch(const csi_handle *h, const float *z, double *out6, float
   for (int j = 0; j < h->model.n_obs; ++j) {
     io.obs[j] = h->d_obs + (long long)j * n;
     io.diag[j] = h->has_diag ? h->d_diag + (long long)j * n : nullptr;
+    io.obsm[h->model.obs_idx[j]] = io.obs[j];
+    io.diagm[h->model.obs_idx[j]] = io.diag[j];
   }
   if (h->has_mh) { io.mh_loc = h->d_mhloc; io.mh_scale = h->d_mhscale; io.mh_logz = h->d_mhlogz; }
   L.partials = h->d_partials;

@@ -65,6 +65,8 @@ struct StarIO {
   float *g[kSlots];
   const float *obs[kMaxObs];
   const float *diag[kMaxObs];   // entries may be null (= 0)
+  const float *obsm[kMaxMean];  // the same columns indexed by the MEAN they observe (null = unobserved); kind diag
+  const float *diagm[kMaxMean];
   const float *mh_loc, *mh_scale, *mh_logz;  // null = constants of DevModel::mh
   const float *z_hyper;         // 5 values (hierarchical only)
   long long n;
@@ -376,7 +378,19 @@ CSI_DEV int grid_locate(const float *g, const unsigned short *lut, float x0, flo
   return i;
 }
 
-// value[b] and d value[b] / d x[d]; out of bounds: value NaN, Jacobian 0 (jnp.where semantics)
+// value[b] and d value[b] / d x[d]; out of bounds: value NaN, Jacobian 0 (jnp.where semantics).
+// The 16 corners are reduced by successive 1-D interpolations (axis 3 first, axis 0 last); the difference
+// vectors of each level are kept, and the derivative along axis d is the same interpolation of the level-d
+// differences over the axes 0..d-1 -- 15 + 11 float4 lerps instead of 16 x (4 x 5) weighted accumulations.
+// D3 = false skips the derivative along axis 3 (Av is a constant of the model: its cotangent is never used).
+struct F4 { float v[4]; };
+CSI_DEV F4 f4_sub(const F4 &a, const F4 &b) { return F4{{a.v[0] - b.v[0], a.v[1] - b.v[1], a.v[2] - b.v[2], a.v[3] - b.v[3]}}; }
+CSI_DEV F4 f4_fma(float t, const F4 &d, const F4 &a) {
+  return F4{{fmaf(t, d.v[0], a.v[0]), fmaf(t, d.v[1], a.v[1]), fmaf(t, d.v[2], a.v[2]), fmaf(t, d.v[3], a.v[3])}};
+}
+CSI_DEV F4 f4_lerp(float t, const F4 &a, const F4 &b) { return f4_fma(t, f4_sub(b, a), a); }
+
+template <bool D3 = true>
 CSI_DEV void grid_eval(const GridDev &gd, const float x[4], float val[4], float jac[4][4]) {
   int idx[4]; float t[4], iw[4]; bool oob = false;
 #pragma unroll
@@ -384,37 +398,37 @@ CSI_DEV void grid_eval(const GridDev &gd, const float x[4], float val[4], float 
     idx[d] = grid_locate(gd.pts[d], gd.lut[d], gd.lut_x0[d], gd.lut_inv[d], gd.shape[d], x[d], t[d], iw[d], oob);
   const long long s3 = 1, s2 = gd.shape[3], s1 = s2 * gd.shape[2], s0 = s1 * gd.shape[1];
   const float4 *base = gd.values + idx[0] * s0 + idx[1] * s1 + idx[2] * s2 + idx[3] * s3;
-  float4 c[16];
+  F4 c[16];  // corner k: bit 3 = axis 0, bit 2 = axis 1, bit 1 = axis 2, bit 0 = axis 3
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
     long long off = ((k >> 3) & 1) * s0 + ((k >> 2) & 1) * s1 + ((k >> 1) & 1) * s2 + (k & 1) * s3;
-    c[k] = __ldg(base + off);
+    const float4 q = __ldg(base + off);
+    c[k] = F4{{q.x, q.y, q.z, q.w}};
+  }
+  F4 e3[8], d3[8], e2[4], d2[4], e1[2], d1[2];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { d3[j] = f4_sub(c[2 * j + 1], c[2 * j]); e3[j] = f4_fma(t[3], d3[j], c[2 * j]); }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { d2[j] = f4_sub(e3[2 * j + 1], e3[2 * j]); e2[j] = f4_fma(t[2], d2[j], e3[2 * j]); }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { d1[j] = f4_sub(e2[2 * j + 1], e2[2 * j]); e1[j] = f4_fma(t[1], d1[j], e2[2 * j]); }
+  const F4 d0 = f4_sub(e1[1], e1[0]);
+  const F4 v = f4_fma(t[0], d0, e1[0]);
+  const F4 g1 = f4_lerp(t[0], d1[0], d1[1]);
+  const F4 g2 = f4_lerp(t[0], f4_lerp(t[1], d2[0], d2[1]), f4_lerp(t[1], d2[2], d2[3]));
+  F4 g3 = F4{{0.f, 0.f, 0.f, 0.f}};
+  if (D3) {
+    const F4 a0 = f4_lerp(t[2], d3[0], d3[1]), a1 = f4_lerp(t[2], d3[2], d3[3]);
+    const F4 a2 = f4_lerp(t[2], d3[4], d3[5]), a3 = f4_lerp(t[2], d3[6], d3[7]);
+    g3 = f4_lerp(t[0], f4_lerp(t[1], a0, a1), f4_lerp(t[1], a2, a3));
   }
 #pragma unroll
-  for (int b = 0; b < 4; ++b) { val[b] = 0.0f; for (int d = 0; d < 4; ++d) jac[b][d] = 0.0f; }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    float w[4];
-#pragma unroll
-    for (int d = 0; d < 4; ++d) w[d] = ((k >> (3 - d)) & 1) ? t[d] : 1.0f - t[d];
-    float sgn[4];
-#pragma unroll
-    for (int d = 0; d < 4; ++d) sgn[d] = ((k >> (3 - d)) & 1) ? iw[d] : -iw[d];
-    float wv = w[0] * w[1] * w[2] * w[3];
-    float wd0 = sgn[0] * w[1] * w[2] * w[3];
-    float wd1 = w[0] * sgn[1] * w[2] * w[3];
-    float wd2 = w[0] * w[1] * sgn[2] * w[3];
-    float wd3 = w[0] * w[1] * w[2] * sgn[3];
-    float cv[4] = {c[k].x, c[k].y, c[k].z, c[k].w};
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      val[b] += cv[b] * wv;
-      jac[b][0] += cv[b] * wd0; jac[b][1] += cv[b] * wd1; jac[b][2] += cv[b] * wd2; jac[b][3] += cv[b] * wd3;
-    }
-  }
-  if (oob) {
-#pragma unroll
-    for (int b = 0; b < 4; ++b) { val[b] = nanf(""); for (int d = 0; d < 4; ++d) jac[b][d] = 0.0f; }
+  for (int b = 0; b < 4; ++b) {
+    val[b] = oob ? nanf("") : v.v[b];
+    jac[b][0] = oob ? 0.0f : d0.v[b] * iw[0];
+    jac[b][1] = oob ? 0.0f : g1.v[b] * iw[1];
+    jac[b][2] = oob ? 0.0f : g2.v[b] * iw[2];
+    jac[b][3] = oob ? 0.0f : g3.v[b] * iw[3];
   }
 }
 
@@ -426,12 +440,13 @@ template <class BcFn>
 CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarState &st, const float o[4],
                       float g_o[4], BcFn &&bc, float *mean_out = nullptr) {
   // observations first: independent loads in flight while the bolometric corrections are gathered
-  float ob_[kMaxObs], dg_[kMaxObs];
+  // (indexed by the mean they observe, so the diagonal likelihood below needs no column search)
+  float ob_[kMaxMean], dg_[kMaxMean];
 #pragma unroll
-  for (int a = 0; a < kMaxObs; ++a) {
-    const bool on = a < m.n_obs;
-    ob_[a] = on ? io.obs[a][i] : 0.0f;
-    dg_[a] = (on && io.diag[a]) ? io.diag[a][i] : 0.0f;
+  for (int k = 0; k < kMaxMean; ++k) {
+    const bool on = m.kind == 0 && io.obsm[k] != nullptr;
+    ob_[k] = on ? io.obsm[k][i] : 0.0f;
+    dg_[k] = (on && io.diagm[k]) ? io.diagm[k][i] : 0.0f;
   }
   float mean[kMaxMean];
   // loc = A @ (o + delta_loc) + B @ params + c
@@ -474,19 +489,15 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
     // Normal(mean[idx], sqrt(var[idx]/tau + diag)).log_prob(obs)   (:231-235)
 #pragma unroll
     for (int k = 0; k < kMaxMean; ++k) {
-      int col = m.col_of_mean[k];
-      if (col >= 0) {
-        float ob = 0.0f, dg = 0.0f;
-#pragma unroll
-        for (int a = 0; a < kMaxObs; ++a)
-          if (a == col) { ob = ob_[a]; dg = dg_[a]; }
+      if (io.obsm[k] != nullptr) {
         float vk = m.var_ext[k] * inv_tau;
-        float s2 = vk + dg;
+        float s2 = vk + dg_[k];
         float inv_s2 = 1.0f / s2;
-        float r = ob - mean[k];
-        ll += -0.5f * r * r * inv_s2 - 0.5f * logf(s2) - kHalfLog2Pi;
-        gm[k] = r * inv_s2;
-        float dl_ds2 = 0.5f * r * r * inv_s2 * inv_s2 - 0.5f * inv_s2;
+        float r = ob_[k] - mean[k];
+        float q = r * inv_s2;
+        ll += -0.5f * r * q - 0.5f * logf(s2) - kHalfLog2Pi;
+        gm[k] = q;
+        float dl_ds2 = 0.5f * (q * q - inv_s2);
         g_tau += dl_ds2 * (-vk * inv_tau);
       }
     }
@@ -497,10 +508,8 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
     float S[kMaxObs * kMaxObs], r[kMaxObs], yv[kMaxObs];
     for (int a = 0; a < k; ++a) {
       int ia = m.obs_idx[a];
-      float dg = 0.0f, oba = 0.0f;
-#pragma unroll
-      for (int a2 = 0; a2 < kMaxObs; ++a2)
-        if (a2 == a) { dg = dg_[a2]; oba = ob_[a2]; }
+      const float oba = io.obs[a][i];
+      const float dg = io.diag[a] ? io.diag[a][i] : 0.0f;
       r[a] = oba - mean[ia];
       for (int b = 0; b < k; ++b)
         S[a * kMaxObs + b] = m.cov_ext[ia * kMaxMean + m.obs_idx[b]] * inv_tau + (a == b ? dg : 0.0f);
@@ -611,10 +620,11 @@ struct BcNone {
 struct BcGrid {  // table interpolation; the Jacobian is formed with the value so corners are gathered once
   const GridDev &gd;
   float jac[4][4];
-  CSI_DEV void forward(const float in[4], float val[4]) { grid_eval(gd, in, val, jac); }
+  CSI_DEV void forward(const float in[4], float val[4]) { grid_eval<false>(gd, in, val, jac); }
   CSI_DEV void vjp(const float gb[4], float gin[4]) {
 #pragma unroll
-    for (int d = 0; d < 4; ++d) gin[d] = gb[0] * jac[0][d] + gb[1] * jac[1][d] + gb[2] * jac[2][d] + gb[3] * jac[3][d];
+    for (int d = 0; d < 3; ++d) gin[d] = gb[0] * jac[0][d] + gb[1] * jac[1][d] + gb[2] * jac[2][d] + gb[3] * jac[3][d];
+    gin[3] = 0.0f;  // Av is a model constant (numpyro_models `const`): its cotangent is never consumed
   }
 };
 

@@ -57,7 +57,8 @@ constexpr uint32_t kStepBytes = 2 * kImgBytes + kBiasBytes;  // hi + lo + bias t
 constexpr uint32_t kKStepBytes = 4096;          // 128 (N) x 16 (K) fp16
 constexpr uint32_t kKStep16 = 512;              // 16 (N) x 16 (K) fp16
 constexpr uint32_t kLbo = 128, kSbo = 256;
-constexpr int kThreads = 320;
+constexpr uint32_t kHalfBytes = 16384;         // one K-half (4 K-steps) of an fp16 128x128 operand image
+constexpr int kThreads = 352;
 constexpr uint32_t kTmemCols = 512;
 constexpr int kGridPtsMax = 512;                // BC table axes kept in shared memory when they fit
 constexpr float kActScale = 512.0f;             // 2^9: activations up to ~127 stay finite in fp16
@@ -80,16 +81,17 @@ constexpr int oBiasA = oGain + 8;       // [1] constant A entry of the bias prod
 constexpr int kSmallFloats = oBiasA + 4;
 
 struct __align__(128) Smem {
-  uint8_t wring[2][kStepBytes];  // weight ring: [buf][hi image | lo image | bias tile]
+  uint8_t wring[2][2][2 * kHalfBytes];  // weight slots: [tile][K-half][hi half | lo half]
+  uint8_t wbias[2][kBiasBytes];         // bias tile of the tile's current forward stage (travels with K-half 0)
   uint8_t resident[kResidentBytes];
   uint8_t a_const[kBiasBytes];   // constant A tile of the bias MMA: columns k = 0..2 hold oBiasA, rest 0
   float small[kSmallFloats];
   uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
   float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
   unsigned short grid_lut[4][kLutBins];
-  uint64_t w_full[2], w_empty[2], a_ready[2], d_ready[2];
+  uint64_t w_full[2][2], w_empty[2][2], a_ready[2], d_ready[2], start_b;
   uint32_t tmem_base;
-  double red[10 * 6];
+  double red[(kThreads / 32) * 6];
   HyperVals hv;
 };
 
@@ -220,6 +222,25 @@ __device__ __forceinline__ void issue_3pass(uint32_t d, uint32_t a_hi, uint32_t 
   }
 }
 
+// one K-half (4 K-steps) of a streamed 128 x 128 contraction, same three products, small terms first within the half
+__device__ __forceinline__ void issue_half(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi, uint32_t b_lo,
+                                           uint32_t idesc, int half, bool bias, uint64_t a_const_desc, uint32_t b_bias) {
+  const uint32_t a_off = 32u * (uint32_t)half;  // 4 K-steps x 8 TMEM columns
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    ptx::mma_f16_ts(d, a_lo + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_hi + (uint32_t)j * kKStepBytes, kLbo, kSbo),
+                    idesc, (half | j) ? 1u : 0u);
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    ptx::mma_f16_ts(d, a_hi + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_lo + (uint32_t)j * kKStepBytes, kLbo, kSbo),
+                    idesc, 1u);
+  if (bias) ptx::mma_f16_ss(d, a_const_desc, ptx::make_smem_desc(b_bias, kLbo, kSbo), idesc, 1);
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    ptx::mma_f16_ts(d, a_hi + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_hi + (uint32_t)j * kKStepBytes, kLbo, kSbo),
+                    idesc, 1u);
+}
+
 // clock64 trace (CSI_TC_DEBUG & 8): recorder `who` of CTA 0 appends (tag, clock) pairs to its 1024-entry region
 struct Tracer {
   long long *p;
@@ -274,11 +295,14 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::fence_proxy_async_smem();  // generic-proxy writes above are read by tcgen05.mma (async proxy)
   if (tid == 0) {
     for (int b = 0; b < 2; ++b) {
-      ptx::mbar_init(&S.w_full[b], 1);
-      ptx::mbar_init(&S.w_empty[b], 2);  // one commit per tile
+      for (int hh = 0; hh < 2; ++hh) {
+        ptx::mbar_init(&S.w_full[b][hh], 1);
+        ptx::mbar_init(&S.w_empty[b][hh], 1);  // one commit: the MMAs of this tile that read the slot
+      }
       ptx::mbar_init(&S.a_ready[b], 4);  // one elected lane per epilogue warp of the tile
       ptx::mbar_init(&S.d_ready[b], 1);
     }
+    ptx::mbar_init(&S.start_b, 1);
     ptx::fence_barrier_init();
     HyperVals h{};
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
@@ -292,22 +316,27 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   const HyperVals hv = S.hv;
   HyperAcc acc{};
 
-  if (warp == 9) {
-    // ===== weight loader: stream the images of the ring stages into the 2-deep ring =====================
+  if (warp >= 9) {
+    // ===== weight loaders: warp 9 + t streams the images of tile slot t, one K-half per slot =============
+    // The two tiles of a CTA run out of phase (see the start gate below), so each has its own stream: slot h of
+    // tile t holds K-steps 4h..4h+3 of the (hi, lo) images of the tile's current 128 x 128 stage and is refilled
+    // with the next stage's half as soon as the MMAs that read it have completed (tcgen05.commit -> w_empty).
+    const int t = warp - 9;
     if (lane == 0) {
-      const long long total = my_pairs * kNRing;
+      const long long total = my_pairs * kNRing * 2;
       for (long long it = 0; it < total; ++it) {
-        const int buf = (int)(it & 1);
-        const int r = (int)(it % kNRing);
-        const uint32_t bytes = r < 5 ? kStepBytes : 2 * kImgBytes;  // only forward images carry a bias tile
-        ptx::mbar_wait(&S.w_empty[buf], (uint32_t)(((it >> 1) & 1) ^ 1));
-        if ((L.tc.debug & 1) && it >= 2) { ptx::mbar_arrive(&S.w_full[buf]); continue; }  // timing experiment
-        ptx::mbar_arrive_expect_tx(&S.w_full[buf], bytes);
-        const uint8_t *src = L.tc.img + (size_t)r * kStepBytes;
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          ptx::bulk_g2s(&S.wring[buf][q * 16384], src + q * 16384, 16384, &S.w_full[buf]);
-        if (r < 5) ptx::bulk_g2s(&S.wring[buf][2 * kImgBytes], src + 2 * kImgBytes, kBiasBytes, &S.w_full[buf]);
+        const int hh = (int)(it & 1);
+        const long long q = it >> 1;           // ring stage counter of this tile
+        const int r = (int)(q % kNRing);
+        const bool with_bias = hh == 0 && r < 5;  // only forward images carry a bias tile
+        ptx::mbar_wait(&S.w_empty[t][hh], (uint32_t)((q & 1) ^ 1));
+        if ((L.tc.debug & 1) && q >= 1) { ptx::mbar_arrive(&S.w_full[t][hh]); continue; }  // timing experiment
+        ptx::mbar_arrive_expect_tx(&S.w_full[t][hh], 2 * kHalfBytes + (with_bias ? kBiasBytes : 0u));
+        const uint8_t *src = L.tc.img + (size_t)r * kStepBytes + (size_t)hh * kHalfBytes;
+        ptx::bulk_g2s(&S.wring[t][hh][0], src, kHalfBytes, &S.w_full[t][hh]);
+        ptx::bulk_g2s(&S.wring[t][hh][kHalfBytes], src + kImgBytes, kHalfBytes, &S.w_full[t][hh]);
+        if (with_bias)
+          ptx::bulk_g2s(&S.wbias[t][0], L.tc.img + (size_t)r * kStepBytes + 2 * kImgBytes, kBiasBytes, &S.w_full[t][hh]);
       }
     }
     __syncwarp();
@@ -324,25 +353,39 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     int s_t[2] = {0, 0};
     long long p_t[2] = {0, 0}, sc_t[2] = {0, 0}, q_t[2] = {0, 0};
     bool done[2] = {my_pairs == 0, my_pairs == 0};
+    constexpr int kGateStage = PREDICT ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
     while (!(done[0] && done[1])) {
 #pragma unroll
       for (int t = 0; t < 2; ++t) {
         if (done[t]) continue;
         const int s = s_t[t];
         const bool ring = ring_stage(s);
-        const int buf = (int)(q_t[t] & 1);
+        const uint32_t wpar = (uint32_t)(q_t[t] & 1);
         if (!ptx::mbar_test_wait(&S.a_ready[t], (uint32_t)(sc_t[t] & 1))) continue;
-        if (ring && !ptx::mbar_test_wait(&S.w_full[buf], (uint32_t)((q_t[t] >> 1) & 1))) continue;
+        if (ring && !ptx::mbar_test_wait(&S.w_full[t][0], wpar)) continue;
         ptx::tc_fence_after();
         tr.rec(1000 + 100 * t + s);
-        if (lane == 0) {
-          const uint32_t w_hi = ptx::smem_u32(&S.wring[buf][0]);
-          const uint32_t d_t = tmem + (uint32_t)t * 256u;
-          const uint32_t a_hi = d_t + 128u, a_lo = d_t + 192u;
-          if (ring) {
-            issue_3pass(d_t, a_hi, a_lo, w_hi, w_hi + kImgBytes, kKStepBytes, idesc128, s <= 5, a_const_desc,
-                        w_hi + 2 * kImgBytes);
-          } else if (s == 0) {
+        const uint32_t d_t = tmem + (uint32_t)t * 256u;
+        const uint32_t a_hi = d_t + 128u, a_lo = d_t + 192u;
+        if (ring) {
+          const uint32_t b_bias = ptx::smem_u32(&S.wbias[t][0]);
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            if (hh == 1) {
+              while (!ptx::mbar_test_wait(&S.w_full[t][1], wpar)) {
+              }
+              ptx::tc_fence_after();
+            }
+            if (lane == 0) {
+              const uint32_t b_hi = ptx::smem_u32(&S.wring[t][hh][0]);
+              issue_half(d_t, a_hi, a_lo, b_hi, b_hi + kHalfBytes, idesc128, hh, hh == 0 && s <= 5, a_const_desc, b_bias);
+              ptx::mma_commit(&S.w_empty[t][hh]);  // the slot (and the bias tile) can be refilled once these complete
+            }
+            __syncwarp();
+          }
+          if (lane == 0) ptx::mma_commit(&S.d_ready[t]);
+        } else if (lane == 0) {
+          if (s == 0) {
             ptx::mma_f16_ts(d_t, a_hi, ptx::make_smem_desc(res + rB0, kLbo, kSbo), idesc128, 0);
             ptx::mma_f16_ts(d_t, a_hi + 8u, ptx::make_smem_desc(res + rB0 + kKStepBytes, kLbo, kSbo), idesc128, 1);
           } else if (s == 6) {
@@ -355,8 +398,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
                         0u);
           }
           ptx::mma_commit(&S.d_ready[t]);
-          if (ring) ptx::mma_commit(&S.w_empty[buf]);  // the slot is free once BOTH tiles' MMAs have read it
         }
+        if (t == 0 && p_t[0] == 0 && s == kGateStage && lane == 0) ptx::mbar_arrive(&S.start_b);
         tr.rec(2000 + 100 * t + s);
         __syncwarp();
         ++sc_t[t];
@@ -389,6 +432,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     if (L.tc.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
       tr.p = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
     long long it = 0;
+    // Start gate: tile B begins a quarter of an evaluation chain after tile A, so that the long CUDA-core phases
+    // of one tile (priors; table gather + likelihood; gradient stores) run under the MMA stages of the other.
+    if (t == 1 && my_pairs > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
     for (long long p = 0; p < my_pairs; ++p) {
       const long long pair = (long long)blockIdx.x + p * gridDim.x;
       const long long i = (pair * 2 + t) * kTile + row;
