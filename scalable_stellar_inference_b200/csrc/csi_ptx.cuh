@@ -133,6 +133,14 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
 }
 
 // ---- tcgen05.mma, kind::f16, A from TMEM, B from shared memory, D in TMEM (cta_group::1) -------------
+// exactly one lane of the (converged) warp: ptxas then issues the tcgen05 ops inside without a per-thread loop
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// shared-memory descriptor from a precomputed low word (address field already shifted) and the constant high word
+__device__ __forceinline__ uint64_t desc_from_words(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
 __device__ __forceinline__ void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
                                            uint32_t accumulate) {
   asm volatile(

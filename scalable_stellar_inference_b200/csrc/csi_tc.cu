@@ -58,7 +58,7 @@ constexpr uint32_t kKStepBytes = 4096;          // 128 (N) x 16 (K) fp16
 constexpr uint32_t kKStep16 = 512;              // 16 (N) x 16 (K) fp16
 constexpr uint32_t kLbo = 128, kSbo = 256;
 constexpr uint32_t kHalfBytes = 16384;         // one K-half (4 K-steps) of an fp16 128x128 operand image
-constexpr int kThreads = 352;
+constexpr int kThreads = 384;  // 8 epilogue warps, 2 MMA issuers (one per tile), 2 weight loaders (one per tile)
 constexpr uint32_t kTmemCols = 512;
 constexpr int kGridPtsMax = 512;                // BC table axes kept in shared memory when they fit
 constexpr float kActScale = 512.0f;             // 2^9: activations up to ~127 stay finite in fp16
@@ -89,7 +89,7 @@ struct __align__(128) Smem {
   uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
   float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
   unsigned short grid_lut[4][kLutBins];
-  uint64_t w_full[2][2], w_empty[2][2], a_ready[2], d_ready[2], start_b;
+  uint64_t w_full[2][2], w_empty[2][2], a_ready[2][2], d_ready[2], start_b;  // a_ready: one barrier per K-half
   uint32_t tmem_base;
   double red[(kThreads / 32) * 6];
   HyperVals hv;
@@ -148,8 +148,8 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&r)[32], float scale, 
     const float v1 = fmaxf(__uint_as_float(r[2 * q + 1]), 0.0f) * scale;
     split2(v0, v1, hi[q], lo[q]);
   }
-  ptx::tmem_st16(a_base + 16 * c, hi);
-  ptx::tmem_st16(a_base + 64 + 16 * c, lo);
+  ptx::tmem_st16(a_base + 32 * c, hi);       // in place over the D chunk just consumed:
+  ptx::tmem_st16(a_base + 32 * c + 16, lo);  // columns [32c, 32c+16) = hi halves, [32c+16, 32c+32) = lo halves
 }
 
 // VJP chunk: D (cotangent before the ReLU mask) -> row scale -> (hi, lo) -> mask on the packed pairs -> A operand
@@ -166,8 +166,8 @@ __device__ __forceinline__ void bwd_chunk(const uint32_t (&r)[32], float f, uint
     hi[2 * s] = h0 & ~ma; lo[2 * s] = l0 & ~ma;
     hi[2 * s + 1] = h1 & ~mb; lo[2 * s + 1] = l1 & ~mb;
   }
-  ptx::tmem_st16(a_base + 16 * c, hi);
-  ptx::tmem_st16(a_base + 64 + 16 * c, lo);
+  ptx::tmem_st16(a_base + 32 * c, hi);       // in place over the D chunk just consumed:
+  ptx::tmem_st16(a_base + 32 * c + 16, lo);  // columns [32c, 32c+16) = hi halves, [32c+16, 32c+32) = lo halves
 }
 
 // power of two f with f * x in [2^9, 2^10) (1 when x is 0 / non-finite)
@@ -185,9 +185,11 @@ __device__ __forceinline__ float pow2_scale(float x) {
 __device__ __forceinline__ uint32_t pack16(uint32_t lo16, uint32_t hi16) { return (lo16 & 0xffffu) | (hi16 << 16); }
 
 // D chunks (4 x 32 columns) through a two-register-set pipeline: the tcgen05.ld of the next chunk is in flight
-// while the current one is processed.  f(r, c) consumes chunk c.
+// while the current one is processed.  f(r, c) consumes chunk c (and may overwrite ITS columns: the A operand of
+// the next stage is written in place, chunk by chunk).
 template <class F>
-__device__ __forceinline__ void for_chunks(uint32_t d_base, F &&f, int ncc = 2) {
+__device__ __forceinline__ void for_chunks(uint32_t d_base, F &&f) {
+  constexpr int ncc = 2;
   uint32_t r0[32], r1[32];
   ptx::tmem_ld32(d_base, r0);
   ptx::tmem_wait_ld_dep(r0);
@@ -202,43 +204,35 @@ __device__ __forceinline__ void for_chunks(uint32_t d_base, F &&f, int ncc = 2) 
   }
 }
 
-// one contraction = A_lo*B_hi + A_hi*B_lo (+ bias) + A_hi*B_hi over 8 K-steps, issued by one thread
-__device__ __forceinline__ void issue_3pass(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi, uint32_t b_lo,
-                                            uint32_t kstep_bytes, uint32_t idesc, bool bias, uint64_t a_const_desc,
-                                            uint32_t b_bias) {
-  uint32_t accumulate = 0;
+// One K-HALF (4 K-steps = 64 contraction indices) of a K = 128 stage, issued as ONE straight-line run of 12 (13)
+// tcgen05.mma: A_lo*B_hi, A_hi*B_lo, (bias), A_hi*B_hi -- small terms first within the half.  Measured on B200
+// (profiles/r1_ubench_issue_patterns.txt): every break in the MMA instruction stream (a loop back-edge, a poll)
+// costs ~250 cycles of tensor-pipe bubble, and per-thread (non-uniform) operands make issue slower than
+// execution; so a run is as long as the pipelining allows, everything is "uniform base + immediate", and each
+// tile has its own issuer warp so that one tile's bubble is filled by the other tile's MMAs.
+// The A operand sits in place in the previous stage's D region: K-step kk has its hi halves at column
+// 32 (kk >> 1) + 8 (kk & 1) and its lo halves 16 columns further.  blo_hi / blo_lo: LOW descriptor words of the
+// B_hi / B_lo images at the half's first K-step (address field = bits 0..13 in 16-byte units: offsets add
+// without carry); KSTEP16 = K-step stride in 16-byte units.
+template <int HH, uint32_t KSTEP16>
+__device__ __forceinline__ void issue_half(uint32_t d, uint32_t a_reg, uint32_t blo_hi, uint32_t blo_lo, uint32_t dhi,
+                                           uint32_t idesc, bool bias, uint64_t a_const_desc, uint64_t bias_desc) {
 #pragma unroll
-  for (int pass = 0; pass < 3; ++pass) {
-    const uint32_t a_sel = pass == 0 ? a_lo : a_hi;
-    const uint32_t b_sel = pass == 1 ? b_lo : b_hi;
-    if (pass == 2 && bias)  // D += c_A * (b_hi + b_lo + b_lolo), exact to ~33 bits
-      ptx::mma_f16_ss(d, a_const_desc, ptx::make_smem_desc(b_bias, kLbo, kSbo), idesc, 1);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      ptx::mma_f16_ts(d, a_sel + 8u * (uint32_t)j, ptx::make_smem_desc(b_sel + (uint32_t)j * kstep_bytes, kLbo, kSbo),
-                      idesc, accumulate);
-      accumulate = 1;
-    }
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t a_lo = a_reg + 32u * (uint32_t)((4 * HH + j) >> 1) + 8u * (uint32_t)(j & 1) + 16u;
+    ptx::mma_f16_ts(d, a_lo, ptx::desc_from_words(blo_hi + (uint32_t)j * KSTEP16, dhi), idesc, (HH | j) ? 1u : 0u);
   }
-}
-
-// one K-half (4 K-steps) of a streamed 128 x 128 contraction, same three products, small terms first within the half
-__device__ __forceinline__ void issue_half(uint32_t d, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi, uint32_t b_lo,
-                                           uint32_t idesc, int half, bool bias, uint64_t a_const_desc, uint32_t b_bias) {
-  const uint32_t a_off = 32u * (uint32_t)half;  // 4 K-steps x 8 TMEM columns
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
-    ptx::mma_f16_ts(d, a_lo + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_hi + (uint32_t)j * kKStepBytes, kLbo, kSbo),
-                    idesc, (half | j) ? 1u : 0u);
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t a_hi = a_reg + 32u * (uint32_t)((4 * HH + j) >> 1) + 8u * (uint32_t)(j & 1);
+    ptx::mma_f16_ts(d, a_hi, ptx::desc_from_words(blo_lo + (uint32_t)j * KSTEP16, dhi), idesc, 1u);
+  }
+  if (bias) ptx::mma_f16_ss(d, a_const_desc, bias_desc, idesc, 1);
 #pragma unroll
-  for (int j = 0; j < 4; ++j)
-    ptx::mma_f16_ts(d, a_hi + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_lo + (uint32_t)j * kKStepBytes, kLbo, kSbo),
-                    idesc, 1u);
-  if (bias) ptx::mma_f16_ss(d, a_const_desc, ptx::make_smem_desc(b_bias, kLbo, kSbo), idesc, 1);
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-    ptx::mma_f16_ts(d, a_hi + a_off + 8u * (uint32_t)j, ptx::make_smem_desc(b_hi + (uint32_t)j * kKStepBytes, kLbo, kSbo),
-                    idesc, 1u);
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t a_hi = a_reg + 32u * (uint32_t)((4 * HH + j) >> 1) + 8u * (uint32_t)(j & 1);
+    ptx::mma_f16_ts(d, a_hi, ptx::desc_from_words(blo_hi + (uint32_t)j * KSTEP16, dhi), idesc, 1u);
+  }
 }
 
 // clock64 trace (CSI_TC_DEBUG & 8): recorder `who` of CTA 0 appends (tag, clock) pairs to its 1024-entry region
@@ -299,7 +293,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         ptx::mbar_init(&S.w_full[b][hh], 1);
         ptx::mbar_init(&S.w_empty[b][hh], 1);  // one commit: the MMAs of this tile that read the slot
       }
-      ptx::mbar_init(&S.a_ready[b], 4);  // one elected lane per epilogue warp of the tile
+      for (int c = 0; c < 2; ++c) ptx::mbar_init(&S.a_ready[b][c], 4);  // one elected lane per epilogue warp
       ptx::mbar_init(&S.d_ready[b], 1);
     }
     ptx::mbar_init(&S.start_b, 1);
@@ -316,12 +310,12 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   const HyperVals hv = S.hv;
   HyperAcc acc{};
 
-  if (warp >= 9) {
-    // ===== weight loaders: warp 9 + t streams the images of tile slot t, one K-half per slot =============
+  if (warp >= 10) {
+    // ===== weight loaders: warp 10 + t streams the images of tile slot t, one K-half per slot =============
     // The two tiles of a CTA run out of phase (see the start gate below), so each has its own stream: slot h of
     // tile t holds K-steps 4h..4h+3 of the (hi, lo) images of the tile's current 128 x 128 stage and is refilled
     // with the next stage's half as soon as the MMAs that read it have completed (tcgen05.commit -> w_empty).
-    const int t = warp - 9;
+    const int t = warp - 10;
     if (lane == 0) {
       const long long total = my_pairs * kNRing * 2;
       for (long long it = 0; it < total; ++it) {
@@ -340,74 +334,90 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       }
     }
     __syncwarp();
-  } else if (warp == 8) {
-    // ===== MMA issuer ===============================================================================
+  } else if (warp >= 8) {
+    // ===== MMA issuers: warp 8 + t issues the tensor work of tile slot t =================================
+    // Everything here is kept PROVABLY warp-uniform (barrier tests through a vote, the TMEM base through a warp
+    // reduction, all addresses derived from parameters, constants and loop counters): ptxas then holds the
+    // tcgen05.mma operands in uniform registers instead of wrapping every UTCHMMA in an elect / R2UR / branch loop.
+    const int t = warp - 8;
+    const uint32_t full = 0xffffffffu;
+    const uint32_t tmem_u = __reduce_or_sync(full, tmem) + (uint32_t)t * 256u;
     const uint32_t idesc128 = ptx::make_idesc_f16(128, 128);
     const uint32_t idesc16 = ptx::make_idesc_f16(128, 16);
     const uint64_t a_const_desc = ptx::make_smem_desc(ptx::smem_u32(S.a_const), kLbo, kSbo);
     const uint32_t res = ptx::smem_u32(S.resident);
-    // The two tiles are served independently: whichever tile has published its A operand (and, for a ring
-    // stage, whose weight image has landed) gets its MMAs issued, so a long CUDA-core stage of one tile (priors,
-    // likelihood, table gathers) never blocks the tensor work of the other.
-    Tracer tr{(L.tc.trace && blockIdx.x == 0 && lane == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
-    int s_t[2] = {0, 0};
-    long long p_t[2] = {0, 0}, sc_t[2] = {0, 0}, q_t[2] = {0, 0};
-    bool done[2] = {my_pairs == 0, my_pairs == 0};
+    // descriptor words, computed once: low word = address field | leading-byte offset, high word = stride | version
+    auto lo_word = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | ((kLbo >> 4) << 16); };
+    const uint32_t dhi = (kSbo >> 4) | (1u << 14);
+    const uint32_t ring_lo = lo_word(ptx::smem_u32(&S.wring[t][0][0]));
+    const uint64_t bias_desc = ptx::make_smem_desc(ptx::smem_u32(&S.wbias[t][0]), kLbo, kSbo);
+    const uint32_t r6_lo = lo_word(res + rB6), r13_lo = lo_word(res + rB13);
+    const uint64_t r6_bias_desc = ptx::make_smem_desc(res + rB6Bias, kLbo, kSbo);
+    const uint64_t r0_desc0 = ptx::make_smem_desc(res + rB0, kLbo, kSbo);
+    const uint64_t r0_desc1 = ptx::make_smem_desc(res + rB0 + kKStepBytes, kLbo, kSbo);
+    const uint64_t r7_desc = ptx::make_smem_desc(res + rB7, kLbo, kSbo);
+    constexpr uint32_t kSlot16 = 2 * kHalfBytes / 16, kLoOff16 = kHalfBytes / 16, kK128 = kKStepBytes / 16, kK16 = kKStep16 / 16;
+    auto wait_bar = [&](uint64_t *bar, uint32_t parity) {
+      while (!__all_sync(full, ptx::mbar_test_wait(bar, parity))) {
+      }
+    };
+    Tracer tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
     constexpr int kGateStage = PREDICT ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
-    while (!(done[0] && done[1])) {
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        if (done[t]) continue;
-        const int s = s_t[t];
+    uint32_t k = 0, q = 0;            // stage counter of the tile's whole life (region parity); streamed-stage counter
+    uint32_t apar0 = 0u, apar1 = 0u;  // parities of the next phases of a_ready[t][0 / 1]
+    for (long long p = 0; p < my_pairs; ++p) {
+#pragma unroll 1
+      for (int s = 0; s < kNStages; ++s, ++k) {
         const bool ring = ring_stage(s);
-        const uint32_t wpar = (uint32_t)(q_t[t] & 1);
-        if (!ptx::mbar_test_wait(&S.a_ready[t], (uint32_t)(sc_t[t] & 1))) continue;
-        if (ring && !ptx::mbar_test_wait(&S.w_full[t][0], wpar)) continue;
-        ptx::tc_fence_after();
+        const uint32_t d_t = tmem_u + (k & 1u) * 128u;             // D of this stage
+        const uint32_t a_reg = tmem_u + ((k & 1u) ^ 1u) * 128u;    // A: in place in the previous stage's D region
+        wait_bar(&S.a_ready[t][0], apar0);
+        apar0 ^= 1u;
         tr.rec(1000 + 100 * t + s);
-        const uint32_t d_t = tmem + (uint32_t)t * 256u;
-        const uint32_t a_hi = d_t + 128u, a_lo = d_t + 192u;
-        if (ring) {
-          const uint32_t b_bias = ptx::smem_u32(&S.wbias[t][0]);
-#pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            if (hh == 1) {
-              while (!ptx::mbar_test_wait(&S.w_full[t][1], wpar)) {
-              }
-              ptx::tc_fence_after();
+        if (s == 0 || s == 7) {
+          if (ptx::elect_one()) {
+            if (s == 0) {
+              ptx::mma_f16_ts(d_t, a_reg, r0_desc0, idesc128, 0);
+              ptx::mma_f16_ts(d_t, a_reg + 8u, r0_desc1, idesc128, 1);
+            } else {
+              ptx::mma_f16_ts(d_t, a_reg, r7_desc, idesc128, 0);
             }
-            if (lane == 0) {
-              const uint32_t b_hi = ptx::smem_u32(&S.wring[t][hh][0]);
-              issue_half(d_t, a_hi, a_lo, b_hi, b_hi + kHalfBytes, idesc128, hh, hh == 0 && s <= 5, a_const_desc, b_bias);
-              ptx::mma_commit(&S.w_empty[t][hh]);  // the slot (and the bias tile) can be refilled once these complete
+            ptx::mma_commit(&S.d_ready[t]);
+          }
+        } else {
+          // K = 128: the A operand arrives in two K-halves; the MMAs of half 0 run under the epilogue of half 1
+          if (ring) wait_bar(&S.w_full[t][0], q & 1u);
+          if (ptx::elect_one()) {
+            if (ring) {
+              issue_half<0, kK128>(d_t, a_reg, ring_lo, ring_lo + kLoOff16, dhi, idesc128, s <= 5, a_const_desc, bias_desc);
+              ptx::mma_commit(&S.w_empty[t][0]);  // slot 0 and the bias tile are refillable once these complete
+            } else if (s == 6) {
+              issue_half<0, kK16>(d_t, a_reg, r6_lo, r6_lo + 8 * kK16, dhi, idesc16, true, a_const_desc, r6_bias_desc);
+            } else {
+              issue_half<0, kK16>(d_t, a_reg, r13_lo, r13_lo + 8 * kK16, dhi, idesc16, false, a_const_desc, r6_bias_desc);
             }
-            __syncwarp();
+            if (t == 0 && p == 0 && s == kGateStage) ptx::mbar_arrive(&S.start_b);
           }
-          if (lane == 0) ptx::mma_commit(&S.d_ready[t]);
-        } else if (lane == 0) {
-          if (s == 0) {
-            ptx::mma_f16_ts(d_t, a_hi, ptx::make_smem_desc(res + rB0, kLbo, kSbo), idesc128, 0);
-            ptx::mma_f16_ts(d_t, a_hi + 8u, ptx::make_smem_desc(res + rB0 + kKStepBytes, kLbo, kSbo), idesc128, 1);
-          } else if (s == 6) {
-            issue_3pass(d_t, a_hi, a_lo, res + rB6, res + rB6 + 8 * kKStep16, kKStep16, idesc16, true, a_const_desc,
-                        res + rB6Bias);
-          } else if (s == 7) {
-            ptx::mma_f16_ts(d_t, a_hi, ptx::make_smem_desc(res + rB7, kLbo, kSbo), idesc128, 0);
-          } else {
-            issue_3pass(d_t, a_hi, a_lo, res + rB13, res + rB13 + 8 * kKStep16, kKStep16, idesc16, false, a_const_desc,
-                        0u);
+          __syncwarp();
+          wait_bar(&S.a_ready[t][1], apar1);
+          apar1 ^= 1u;
+          if (ring) wait_bar(&S.w_full[t][1], q & 1u);
+          if (ptx::elect_one()) {
+            if (ring) {
+              issue_half<1, kK128>(d_t, a_reg, ring_lo + kSlot16, ring_lo + kSlot16 + kLoOff16, dhi, idesc128, false,
+                                   a_const_desc, bias_desc);
+              ptx::mma_commit(&S.w_empty[t][1]);
+            } else if (s == 6) {
+              issue_half<1, kK16>(d_t, a_reg, r6_lo + 4 * kK16, r6_lo + 12 * kK16, dhi, idesc16, false, a_const_desc, r6_bias_desc);
+            } else {
+              issue_half<1, kK16>(d_t, a_reg, r13_lo + 4 * kK16, r13_lo + 12 * kK16, dhi, idesc16, false, a_const_desc, r6_bias_desc);
+            }
+            ptx::mma_commit(&S.d_ready[t]);
           }
-          ptx::mma_commit(&S.d_ready[t]);
+          if (ring) ++q;
         }
-        if (t == 0 && p_t[0] == 0 && s == kGateStage && lane == 0) ptx::mbar_arrive(&S.start_b);
-        tr.rec(2000 + 100 * t + s);
         __syncwarp();
-        ++sc_t[t];
-        if (ring) ++q_t[t];
-        if (++s_t[t] == kNStages) {
-          s_t[t] = 0;
-          if (++p_t[t] == my_pairs) done[t] = true;
-        }
+        tr.rec(2000 + 100 * t + s);
       }
     }
   } else {
@@ -415,18 +425,23 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     const int t = warp >> 2;                   // tile slot within the pair
     const int row = (warp & 3) * 32 + lane;    // TMEM lane == row of the tile
     const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
-    const uint32_t d_base = tmem + lane_base + (uint32_t)t * 256u;
-    const uint32_t a_base = d_base + 128u;
+    // TMEM of a tile: two 128-column regions.  Stage k (counted over the tile's whole life, `it`) accumulates D
+    // into region k & 1; its epilogue converts D into the next stage's A operand IN PLACE, so stage k + 1 reads A
+    // from region k & 1 and accumulates into the other one.  Because A appears chunk by chunk, the MMAs of the
+    // next stage start on K-chunk c while the epilogue is still converting chunk c + 1.
+    const uint32_t t_base = tmem + lane_base + (uint32_t)t * 256u;
     const float *sm = S.small;
     const float inv_fwd = 1.0f / (kActScale * L.tc.w_scale);
     const float inv_wscale = 1.0f / L.tc.w_scale;
     uint32_t *mask = &S.mask[0][tid];  // sign word of chunk c of hidden layer h at mask[(h * 4 + c) * 256]
     // hand the A operand to the MMA warp: all tcgen05.st of this warp done, then one elected arrive
-    auto publish_a = [&]() {
+    // (one barrier per K-half: a half's next phase belongs to the next stage, which cannot begin before the MMA
+    // warp has consumed this one, so the producer can never run two phases ahead of the consumer's parity)
+    auto publish_a = [&](int c) {
       ptx::tmem_wait_st();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&S.a_ready[t]);
+      if (lane == 0) ptx::mbar_arrive(&S.a_ready[t][c]);
     };
     Tracer tr{nullptr, 0};
     if (L.tc.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
@@ -482,9 +497,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         a0[8] = ca16 | (ca16 << 16);
 #pragma unroll
         for (int q = 9; q < 16; ++q) a0[q] = 0u;
-        ptx::tmem_st16(a_base, a0);
+        ptx::tmem_st16(t_base + (uint32_t)(((it & 1) ^ 1) * 128), a0);  // A of stage `it` lives in the other region
       }
-      publish_a();
+      publish_a(0);
 
       float un = 1.0f;    // cotangent un-scaling: true value = D * un
       float amax = 0.0f;  // max |A operand| of the current VJP stage (after scaling)
@@ -493,6 +508,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         tr.rec(100 + s);
         ptx::mbar_wait(&S.d_ready[t], (uint32_t)(it & 1));
         ptx::tc_fence_after();
+        const uint32_t d_base = t_base + (uint32_t)((it & 1) * 128);
+        const uint32_t a_base = d_base;
         tr.rec(200 + s);
         if (s <= 5) {
           // ---- pre-activations of hidden layer s (bias already in D) -> sign word, ReLU -> next A operand ----
@@ -500,7 +517,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
           for_chunks(d_base, [&](const uint32_t (&r)[32], int c) {
             mk[c * 256] = sign_word(r);
             fwd_chunk(r, inv_wscale, a_base, c);
-          }, (L.tc.debug & 4) ? 1 : 2);
+            if (c & 1) publish_a(c >> 1);  // K-half c >> 1 of the next stage's A operand is complete
+          });
         } else if (s == 6) {
           // ---- emulator outputs -> predict + likelihood -> cotangent of the outputs -> A operand of stage 7 ----
           uint32_t r8[8];
@@ -555,7 +573,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             for (int e = 0; e < 32; e += 2)
               mx = fmaxf(mx, fmaxf(fabsf(__uint_as_float(r[e])), fabsf(__uint_as_float(r[e + 1]))));
             bwd_chunk(r, f, mk[c * 256], a_base, c);
-          }, (L.tc.debug & 4) ? 1 : 2);
+            if (c & 1) publish_a(c >> 1);
+          });
           amax = mx * f;
           un = un / f * inv_wscale;
         } else {
@@ -572,10 +591,10 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
           }
         }
         tr.rec(300 + s);
-        if (s < kNStages - 1) {
-          publish_a();
+        if (s == 6 && !PREDICT) {
+          publish_a(0);  // the narrow A operand of stage 7 (the 128-wide stages publish chunk by chunk above)
           tr.rec(400 + s);
-        } else {
+        } else if (s == kNStages - 1) {
           // all reads of D are complete (wait::ld above); order them before the next pair's MMAs
           ptx::tc_fence_before();
         }
@@ -583,7 +602,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     }
   }
 
-  // ---- teardown + reduction (all 320 threads) -----------------------------------------------------------
+  // ---- teardown + reduction (all threads) -----------------------------------------------------------
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);

@@ -12,7 +12,7 @@ using namespace csi;
 
 struct __align__(128) USmem {
   uint8_t b_img[65536];
-  uint64_t bar, bar2;
+  uint64_t bar, bar2, bar3, bar4, bar5;
   uint32_t tmem_base;
 };
 
@@ -127,13 +127,60 @@ __global__ void __launch_bounds__(160) ubench_kernel(long long *out) {
     if (tid == 128 && busy) { ptx::mbar_wait(&S.bar, par); par ^= 1; }
     __syncthreads();
   }
+  // ---- issue-pattern variants: 32 batches of 6 MMAs (immediate operands), whole warp 4 in the loop -----------
+  //  0: elected lane issues, __syncwarp            1: + vote(mbarrier.test_wait) on a completed barrier before each batch
+  //  2: variant 1 + clock64/global store per batch  3: variant 0 + tcgen05.commit (unwaited barrier) after each batch
+  //  4: batches of 24 MMAs x 8 (same total)         5: variant 1 with a failing poll of a second barrier as well
+  //  6: single thread (tid 128 only), 6-MMA batches, no warp-level ops
+  {
+    const uint32_t idesc = ptx::make_idesc_f16(128, 128);
+    const uint32_t lo0 = ((b_s & 0x3FFFFu) >> 4) | ((128u >> 4) << 16), dhi = (256u >> 4) | (1u << 14);
+    if (tid == 0) { ptx::mbar_init(&S.bar3, 1); ptx::mbar_init(&S.bar4, 1); ptx::mbar_init(&S.bar5, 1); ptx::fence_barrier_init(); }
+    __syncthreads();
+    if (tid == 0) ptx::mbar_arrive(&S.bar3);  // bar3: phase 0 complete -> test_wait(parity 0) succeeds; bar4 never completes
+    __syncthreads();
+    for (int v = 0; v < 7; ++v) {
+      __syncthreads();
+      if (warp == 4 && (v != 6 || lane == 0)) {
+        long long t0 = clock64();
+        const int nb = (v == 4) ? 8 : 32;
+        for (int bt = 0; bt < nb; ++bt) {
+          bool ok = true;
+          if (v == 1 || v == 2 || v == 5) ok = __all_sync(0xffffffffu, ptx::mbar_test_wait(&S.bar3, 0u));
+          if (v == 5) ok = ok && !__all_sync(0xffffffffu, ptx::mbar_test_wait(&S.bar4, 0u));
+          if (!ok) continue;
+          if (v == 6 || ptx::elect_one()) {
+            if (v == 4) {
+#pragma unroll
+              for (int j = 0; j < 24; ++j)
+                ptx::mma_f16_ts(tmem, tmem + 128u + 8u * (j & 7), ptx::desc_from_words(lo0 + 256u * (j & 7), dhi), idesc, 1u);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 6; ++j)
+                ptx::mma_f16_ts(tmem, tmem + 128u + 8u * j, ptx::desc_from_words(lo0 + 256u * j, dhi), idesc, 1u);
+            }
+            if (v == 3) ptx::mma_commit(&S.bar5);
+            if (v == 2) { out[40 + (bt & 3)] = clock64(); }
+          }
+          if (v != 6) __syncwarp();
+        }
+        if (lane == 0) {
+          ptx::mma_commit(&S.bar);
+          ptx::mbar_wait(&S.bar, par);
+          out[30 + v] = clock64() - t0;
+        }
+      }
+      par ^= 1;
+      __syncthreads();
+    }
+  }
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 4) ptx::tmem_dealloc<512>(tmem);
 }
 
 int main() {
-  long long *d, h[32] = {0};
+  long long *d, h[48] = {0};
   cudaMalloc(&d, sizeof(h));
   cudaMemset(d, 0, sizeof(h));
   const int smem = (int)sizeof(USmem) + 1024;
@@ -155,5 +202,6 @@ int main() {
   for (int busy = 0; busy < 2; ++busy)
     printf("4 warps, tensor pipe %s: tcgen05.ld x32 + wait + use %lld cyc, 2 x tcgen05.st x16 + wait %lld cyc\n",
            busy ? "busy (MMA N=128 stream)" : "idle", h[14 + busy * 3], h[15 + busy * 3]);
+  for (int v = 0; v < 7; ++v) printf("issue-pattern variant %d: %.1f cyc/MMA\n", v, h[30 + v] / 192.0);
   return 0;
 }
