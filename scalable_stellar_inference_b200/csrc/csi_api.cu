@@ -1,6 +1,7 @@
 // csi_api.cu -- the C ABI of libcsi (include/csi.h): handle management, constant preparation, data upload
 // and the stream-ordered evaluation entry points.  No CPU fallback: creation fails without an sm_100 device.
 #include <math.h>
+#include <cmath>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -213,7 +214,7 @@ static int upload_net(csi_handle *h, const csi_net &n, NetDev &d) {
   return CSI_OK;
 }
 
-static int upload_grid(csi_handle *h, const csi_grid &g, int bands, GridDev &d) {
+static int upload_grid(csi_handle *h, const csi_grid &g, int bands, float av, GridDev &d) {
   memset(&d, 0, sizeof(d));
   size_t nn = 1;
   for (int a = 0; a < 4; ++a) {
@@ -251,6 +252,30 @@ static int upload_grid(csi_handle *h, const csi_grid &g, int bands, GridDev &d) 
   float4 *dv; int rc;
   if ((rc = dev_upload(h, v, &dv))) return rc;
   d.values = dv;
+  // Av-collapsed copy for the potential (GridDev::values3): locate `av` on axis 3 and interpolate every (T, g, F)
+  // node along it with the SAME fp32 operations as the first level of grid_eval (fmaf(t, c1 - c0, c0)), so the
+  // 3-D path returns bit-identical values to the 4-D one.
+  {
+    const int n3 = g.shape[3];
+    std::vector<float> p3(g.points[3], g.points[3] + n3);
+    const float x = av;
+    int i3 = 0;
+    while (i3 < n3 - 2 && p3[i3 + 1] < x) ++i3;
+    const float g0 = p3[i3], g1 = p3[i3 + 1];
+    const float iw = 1.0f / (g1 - g0);
+    const float t3 = (x - g0) * iw;
+    d.av_oob = (x < p3.front() || x > p3.back() || !(x == x)) ? 1 : 0;
+    const size_t n012 = nn / (size_t)n3;
+    std::vector<float4> v3(n012);
+    for (size_t j = 0; j < n012; ++j) {
+      const float4 c0 = v[j * n3 + i3], c1 = v[j * n3 + i3 + 1];
+      v3[j] = make_float4(std::fmaf(t3, c1.x - c0.x, c0.x), std::fmaf(t3, c1.y - c0.y, c0.y),
+                          std::fmaf(t3, c1.z - c0.z, c0.z), std::fmaf(t3, c1.w - c0.w, c0.w));
+    }
+    float4 *dv3;
+    if ((rc = dev_upload(h, v3, &dv3))) return rc;
+    d.values3 = dv3;
+  }
   return CSI_OK;
 }
 
@@ -288,7 +313,7 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
     rc = fail(CSI_EINVAL, "bc_mode net without bc_net weights");
   }
   if (rc == CSI_OK && cfg->bc_grid.shape[0] > 0) {
-    rc = upload_grid(h, cfg->bc_grid, std::max(cfg->bands, 1), h->grid);
+    rc = upload_grid(h, cfg->bc_grid, std::max(cfg->bands, 1), (float)cfg->av, h->grid);
   } else if (rc == CSI_OK && cfg->bands > 0 && cfg->bc_mode == CSI_BC_GRID) {
     rc = fail(CSI_EINVAL, "bc_mode grid without a table");
   }

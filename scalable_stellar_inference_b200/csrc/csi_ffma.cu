@@ -53,9 +53,11 @@ __global__ void __launch_bounds__(kRows) potential_ffma_kernel(const __grid_cons
     float *mean_out = nullptr;
     float mean_local[kMaxMean];
     if (PREDICT) mean_out = mean_local;
-    if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, mean_out); }
-    if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc, mean_out); }
-    if (BC == 2) { BcNetFfma bc{L.bcnet, S.bufA, S.bufB, S.bcmask, tid}; star_mid(m, io, i, st, o, g_o, bc, mean_out); }
+    StarObs so;
+    star_load_obs(m, io, i, so);
+    if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mean_out); }
+    if (BC == 1) { BcGrid bc{L.grid}; star_mid(m, io, i, st, o, g_o, bc, so, mean_out); }
+    if (BC == 2) { BcNetFfma bc{L.bcnet, S.bufA, S.bufB, S.bcmask, tid}; star_mid(m, io, i, st, o, g_o, bc, so, mean_out); }
     if (PREDICT) {
       if (L.mean_out) {
 #pragma unroll

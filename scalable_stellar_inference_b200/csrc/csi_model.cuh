@@ -80,6 +80,11 @@ struct GridDev {
   const unsigned short *lut[4];  // [kLutBins] per axis: an interval index <= the answer for every x of the bin
   float lut_x0[4], lut_inv[4];   // bin = (x - lut_x0) * lut_inv
   const float4 *values;  // [n0*n1*n2*n3]
+  // The potential always evaluates the table at the model constant Av (numpyro_models `const`), so the table is
+  // interpolated along axis 3 ONCE at creation (same fp32 arithmetic as grid_eval's first level): the per-star work
+  // is then a 3-D interpolation, 8 gathers instead of 16.  null when not built; av_oob = Av outside the axis.
+  const float4 *values3;  // [n0*n1*n2]
+  int av_oob;
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -153,6 +158,20 @@ CSI_DEV void tn_site(const TnC &c, float u, float loc, float scale, float logz, 
 }
 
 // log TN(x; mu, sigma, low, high) and partials wrt x, mu, sigma (finite bounds)
+// (inv = 1 / sigma and logsig = log sigma are passed in: they are per-evaluation constants in the hierarchical model)
+CSI_DEV void tn_logpdf_grads_pre(float x, float mu, float inv, float logsig, float low, float high, float &lp,
+                                 float &dx, float &dmu, float &dsig) {
+  float alpha = (low - mu) * inv, beta = (high - mu) * inv;
+  float logz, ra, rb;
+  log_ndtr_diff(alpha, beta, logz, ra, rb);
+  float r = (x - mu) * inv;
+  lp = -0.5f * r * r - logsig - kHalfLog2Pi - logz;
+  float dlogz_dmu = -(rb - ra) * inv;
+  float dlogz_dsig = -(beta * rb - alpha * ra) * inv;
+  dx = -r * inv;
+  dmu = r * inv - dlogz_dmu;
+  dsig = (r * r - 1.0f) * inv - dlogz_dsig;
+}
 CSI_DEV void tn_logpdf_grads(float x, float mu, float sigma, float low, float high, float &lp, float &dx,
                              float &dmu, float &dsig) {
   float inv = 1.0f / sigma;
@@ -183,6 +202,9 @@ struct HyperVals {
   float ddydz, dmu_a;   // dvalue/du of the two interval sites
   float prior_lp;       // sum of the 5 hyper log-terms
   float gprior[5];      // d prior_lp / du
+  // truncation terms of a_MLT ~ TN(mu_a, sigma_a, a_lo, a_hi): they depend on the hyper-parameters only
+  float a_inv, a_logsig, a_alpha, a_beta, a_logz, a_ra, a_rb;
+  float y_inv, y_logsig;  // 1 / sigma_Y, log sigma_Y
 };
 
 CSI_DEV void hyper_eval(const DevModel &m, const float *zh, HyperVals &h) {
@@ -205,6 +227,13 @@ CSI_DEV void hyper_eval(const DevModel &m, const float *zh, HyperVals &h) {
   lp += lt; h.gprior[4] = dlt;
   h.sigma_a = rsqrtf(pa);
   h.prior_lp = lp;
+  h.a_inv = 1.0f / h.sigma_a;
+  h.a_logsig = logf(h.sigma_a);
+  h.a_alpha = (m.a_lo - h.mu_a) * h.a_inv;
+  h.a_beta = (m.a_hi - h.mu_a) * h.a_inv;
+  log_ndtr_diff(h.a_alpha, h.a_beta, h.a_logz, h.a_ra, h.a_rb);
+  h.y_inv = 1.0f / h.sigma_y;
+  h.y_logsig = logf(h.sigma_y);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -226,16 +255,23 @@ struct HyperAcc {  // per-thread partial sums of dlogp/d(y0, dydz, sigma_y, mu_a
   double g[5];
 };
 
-CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, long long i, StarState &st,
-                      HyperAcc &acc) {
-  float lp = 0.0f;
-  // every input of this star first: independent global loads in flight together
+// the inputs of star_pre, loaded ahead of use so that their latency hides under the preceding MMA stage
+struct StarIn {
   float zv[kSlots];
+  float mloc, mscale, mlogz;
+};
+CSI_DEV void star_load_z(const DevModel &m, const StarIO &io, long long i, StarIn &in) {
 #pragma unroll
-  for (int s = 0; s < kSlots; ++s) zv[s] = io.z[s] ? io.z[s][i] : 0.0f;
-  const float mloc = io.mh_loc ? io.mh_loc[i] : m.mh.loc;
-  const float mscale = io.mh_scale ? io.mh_scale[i] : m.mh.scale;
-  const float mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.logz;
+  for (int s = 0; s < kSlots; ++s) in.zv[s] = io.z[s] ? io.z[s][i] : 0.0f;
+  in.mloc = io.mh_loc ? io.mh_loc[i] : m.mh.loc;
+  in.mscale = io.mh_scale ? io.mh_scale[i] : m.mh.scale;
+  in.mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.logz;
+}
+
+CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, StarState &st, HyperAcc &acc) {
+  float lp = 0.0f;
+  const float *zv = in.zv;
+  const float mloc = in.mloc, mscale = in.mscale, mlogz = in.mlogz;
 #pragma unroll
   for (int s = 0; s < kSlots; ++s) st.gp[s] = 0.0f;
   // scaled_precision ~ Gamma(df/2, df/2)   (:195-196 / :301-302)
@@ -274,7 +310,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     float y = m.y_lo + m.y_w * sy;
     float dy = m.y_w * sy * (1.0f - sy);
     float lpy, dl_dy, dl_dmu, dl_dsig;
-    tn_logpdf_grads(y, mu_y, h.sigma_y, m.y_lo, m.y_hi, lpy, dl_dy, dl_dmu, dl_dsig);
+    tn_logpdf_grads_pre(y, mu_y, h.y_inv, h.y_logsig, m.y_lo, m.y_hi, lpy, dl_dy, dl_dmu, dl_dsig);
     lp += lpy + m.log_y_w + log_sigmoid_prod(uy);
     st.gp[S_Y] = dl_dy * dy + (1.0f - 2.0f * sy);
     g_mh_prior += dl_dmu * dmu_df * h.dydz * dq_dmh;
@@ -286,8 +322,12 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
     float sa = sigmoidf_(ua);
     float a = m.a_lo + m.a_w * sa;
     float da = m.a_w * sa * (1.0f - sa);
-    float lpa, dl_da, dl_dmua, dl_dsiga;
-    tn_logpdf_grads(a, h.mu_a, h.sigma_a, m.a_lo, m.a_hi, lpa, dl_da, dl_dmua, dl_dsiga);
+    // TN(mu_a, sigma_a) has the same normaliser for every star: evaluated once in hyper_eval
+    const float ra_ = (a - h.mu_a) * h.a_inv;
+    const float lpa = -0.5f * ra_ * ra_ - h.a_logsig - kHalfLog2Pi - h.a_logz;
+    const float dl_da = -ra_ * h.a_inv;
+    const float dl_dmua = ra_ * h.a_inv + (h.a_rb - h.a_ra) * h.a_inv;
+    const float dl_dsiga = (ra_ * ra_ - 1.0f) * h.a_inv + (h.a_beta * h.a_rb - h.a_alpha * h.a_ra) * h.a_inv;
     lp += lpa + m.log_a_w + log_sigmoid_prod(ua);
     st.gp[S_A] = dl_da * da + (1.0f - 2.0f * sa);
     acc.g[3] += (double)dl_dmua;
@@ -356,6 +396,13 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, l
   }
   st.lp = lp;
   st.g_logmass = 0.0f; st.g_mh_dir = 0.0f; st.g_tau_lik = 0.0f; st.g_dist = 0.0f;
+}
+
+CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIO &io, long long i, StarState &st,
+                      HyperAcc &acc) {
+  StarIn in;
+  star_load_z(m, io, i, in);
+  star_pre(m, h, in, st, acc);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -432,22 +479,80 @@ CSI_DEV void grid_eval(const GridDev &gd, const float x[4], float val[4], float 
   }
 }
 
+// The same interpolation on the Av-collapsed table (GridDev::values3): 3 axes, 8 corners.  The three axis searches
+// run interleaved (their lookup-table and axis loads are independent), one combined walk loop.
+CSI_DEV void grid_eval3(const GridDev &gd, const float x[4], float val[4], float jac[4][4]) {
+  int idx[3]; float g1[3], t[3], iw[3];
+  bool oob = gd.av_oob != 0;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    int b = (int)((x[d] - gd.lut_x0[d]) * gd.lut_inv[d]) - 1;
+    b = min(max(b, 0), kLutBins - 1);
+    idx[d] = (x[d] == x[d]) ? (int)gd.lut[d][b] : 0;
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) g1[d] = gd.pts[d][idx[d] + 1];
+  bool more = true;
+  while (more) {
+    more = false;
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+      if (idx[d] < gd.shape[d] - 2 && g1[d] < x[d]) { ++idx[d]; g1[d] = gd.pts[d][idx[d] + 1]; more = true; }
+  }
+  const long long s2 = 1, s1 = gd.shape[2], s0 = s1 * gd.shape[1];
+  const float4 *base = gd.values3 + idx[0] * s0 + idx[1] * s1 + idx[2] * s2;
+  F4 e3[8];  // corner j: bit 2 = axis 0, bit 1 = axis 1, bit 0 = axis 2
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 q = __ldg(base + ((j >> 2) & 1) * s0 + ((j >> 1) & 1) * s1 + (j & 1) * s2);
+    e3[j] = F4{{q.x, q.y, q.z, q.w}};
+  }
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const float g0 = gd.pts[d][idx[d]];
+    iw[d] = 1.0f / (g1[d] - g0);
+    t[d] = (x[d] - g0) * iw[d];
+    oob = oob || (x[d] < gd.pts[d][0]) || (x[d] > gd.pts[d][gd.shape[d] - 1]) || !(x[d] == x[d]);
+  }
+  F4 e2[4], d2[4], e1[2], d1[2];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { d2[j] = f4_sub(e3[2 * j + 1], e3[2 * j]); e2[j] = f4_fma(t[2], d2[j], e3[2 * j]); }
+#pragma unroll
+  for (int j = 0; j < 2; ++j) { d1[j] = f4_sub(e2[2 * j + 1], e2[2 * j]); e1[j] = f4_fma(t[1], d1[j], e2[2 * j]); }
+  const F4 d0 = f4_sub(e1[1], e1[0]);
+  const F4 v = f4_fma(t[0], d0, e1[0]);
+  const F4 gg1 = f4_lerp(t[0], d1[0], d1[1]);
+  const F4 gg2 = f4_lerp(t[0], f4_lerp(t[1], d2[0], d2[1]), f4_lerp(t[1], d2[2], d2[3]));
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+    val[b] = oob ? nanf("") : v.v[b];
+    jac[b][0] = oob ? 0.0f : d0.v[b] * iw[0];
+    jac[b][1] = oob ? 0.0f : gg1.v[b] * iw[1];
+    jac[b][2] = oob ? 0.0f : gg2.v[b] * iw[2];
+    jac[b][3] = 0.0f;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // predict + likelihood (numpyro_models.py:203-240), photometry (_jax/star.py:39-65)
 // BcFn: object with forward(const float in[4], float val[4]) and vjp(const float gb[4], float gin[4])
 // ---------------------------------------------------------------------------------------------
-template <class BcFn>
-CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarState &st, const float o[4],
-                      float g_o[4], BcFn &&bc, float *mean_out = nullptr) {
-  // observations first: independent loads in flight while the bolometric corrections are gathered
-  // (indexed by the mean they observe, so the diagonal likelihood below needs no column search)
-  float ob_[kMaxMean], dg_[kMaxMean];
+// observations of star i for the diagonal likelihood, indexed by the mean they observe (no column search);
+// loaded ahead of star_mid so that their latency hides under the last forward MMA stage
+struct StarObs { float ob[kMaxMean], dg[kMaxMean]; };
+CSI_DEV void star_load_obs(const DevModel &m, const StarIO &io, long long i, StarObs &so) {
 #pragma unroll
   for (int k = 0; k < kMaxMean; ++k) {
     const bool on = m.kind == 0 && io.obsm[k] != nullptr;
-    ob_[k] = on ? io.obsm[k][i] : 0.0f;
-    dg_[k] = (on && io.diagm[k]) ? io.diagm[k][i] : 0.0f;
+    so.ob[k] = on ? io.obsm[k][i] : 0.0f;
+    so.dg[k] = (on && io.diagm[k]) ? io.diagm[k][i] : 0.0f;
   }
+}
+
+template <class BcFn>
+CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarState &st, const float o[4],
+                      float g_o[4], BcFn &&bc, const StarObs &so, float *mean_out = nullptr) {
+  const float *ob_ = so.ob, *dg_ = so.dg;
   float mean[kMaxMean];
   // loc = A @ (o + delta_loc) + B @ params + c
   mean[0] = o[0] + m.cc[0];
@@ -620,7 +725,10 @@ struct BcNone {
 struct BcGrid {  // table interpolation; the Jacobian is formed with the value so corners are gathered once
   const GridDev &gd;
   float jac[4][4];
-  CSI_DEV void forward(const float in[4], float val[4]) { grid_eval<false>(gd, in, val, jac); }
+  CSI_DEV void forward(const float in[4], float val[4]) {
+    if (gd.values3 != nullptr) grid_eval3(gd, in, val, jac);  // in[3] is the model constant the table was collapsed at
+    else grid_eval<false>(gd, in, val, jac);
+  }
   CSI_DEV void vjp(const float gb[4], float gin[4]) {
 #pragma unroll
     for (int d = 0; d < 3; ++d) gin[d] = gb[0] * jac[0][d] + gb[1] * jac[1][d] + gb[2] * jac[2][d] + gb[3] * jac[3][d];

@@ -531,9 +531,11 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             for (int c = 0; c < 4; ++c) o[c] = sm[oOutLoc + c] + sm[oOutScale + c] * (__uint_as_float(r8[c]) * inv_fwd);
             float mean_local[kMaxMean];
             float *mo = PREDICT ? mean_local : nullptr;
+            StarObs so;
+            star_load_obs(m, io, i, so);
             if (L.tc.debug & 2) { g_o[0] = o[0]; g_o[1] = o[1]; g_o[2] = o[2]; g_o[3] = o[3]; }
-            else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, mo); }
-            else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, mo); }
+            else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
+            else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
 #pragma unroll
             for (int c = 0; c < 4; ++c) g_y[c] = g_o[c] * sm[oOutScale + c];
             if (PREDICT) {
