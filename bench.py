@@ -57,6 +57,16 @@ def measured_peaks():
     return 1590.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of THIS command
+    (profiles/potential_ncu.json, written by tools/ncu_to_json.py); None when no capture is committed."""
+    p = os.path.join(ROOT, "profiles", "potential_ncu.json")
+    if not os.path.exists(p):
+        return None, None
+    d = json.load(open(p))
+    return d.get("dram_read_bytes", 0) + d.get("dram_write_bytes", 0), d
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -251,6 +261,9 @@ def run_b200(args):
         kern = float(kern_ms.mean())
         stars_local = model.n_local
         achieved = FLOP_PER_STAR * stars_local / (kern * 1e-3) / 1e12
+        traffic, ncu = ncu_traffic()
+        if ncu is not None and (ncu.get("stars") != stars_local or world != 1):
+            traffic = None  # the capture is of the 1-GPU, 1 M-star launch only
         line = {
             "metric": "logp+grad evals/s", "value": 1e3 / ms_per_step, "unit": "evals/s", "n_gpus": world,
             "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -262,7 +275,9 @@ def run_b200(args):
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
-                         "frac": achieved / bf16_peak, "traffic": None,
+                         "frac": achieved / bf16_peak, "traffic": traffic,
+                         "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full)",
+                         "algorithmic_bytes": 29 * 4 * stars_local,
                          "kernel": "potential_tc_kernel" if args.engine == "tcgen05" else "potential_ffma_kernel",
                          "kernel_ms": kern, "stars_per_launch": stars_local, "flop_per_star": FLOP_PER_STAR,
                          "peak_source": which + "; fp16/bf16 dense tensor peak",

@@ -61,7 +61,10 @@ static bool make_tn(const csi_tn &t, TnC &o) {
   o.loc = (float)t.loc; o.scale = (float)t.scale; o.low = (float)t.low; o.high = (float)t.high;
   bool lo = std::isfinite(t.low), hi = std::isfinite(t.high);
   o.kind = lo && hi ? TN_INTERVAL : hi ? TN_UPPER : lo ? TN_LOWER : TN_REAL;
-  o.logz = (float)tn_logz(t.loc, t.scale, t.low, t.high);
+  const double lz = tn_logz(t.loc, t.scale, t.low, t.high);
+  o.logz = (float)lz;
+  o.inv_scale = (float)(1.0 / t.scale);
+  o.lognorm = (float)(lz + log(t.scale));
   o.logw = lo && hi ? (float)log(t.high - t.low) : 0.0f;
   return true;
 }
@@ -428,9 +431,10 @@ extern "C" int csi_set_data(csi_handle *h, int64_t n, const double *obs, const d
     const TnC &tn = h->model.mh;
     for (int64_t i = 0; i < n; ++i) {
       if (!(mh_scale[i] > 0)) return fail(CSI_EINVAL, "mh_scale must be > 0");
-      a[i] = (float)mh_loc[i]; b[i] = (float)mh_scale[i];
-      c[i] = (float)tn_logz(mh_loc[i], mh_scale[i], tn.kind & 1 ? (double)tn.low : -INFINITY,
-                            tn.kind & 2 ? (double)tn.high : INFINITY);
+      // device arrays: loc, 1 / scale, logz + log(scale)  (see StarIO::mh_*)
+      a[i] = (float)mh_loc[i]; b[i] = (float)(1.0 / mh_scale[i]);
+      c[i] = (float)(tn_logz(mh_loc[i], mh_scale[i], tn.kind & 1 ? (double)tn.low : -INFINITY,
+                             tn.kind & 2 ? (double)tn.high : INFINITY) + log(mh_scale[i]));
     }
     CK(cudaMalloc(&h->d_mhloc, n * sizeof(float)));
     CK(cudaMalloc(&h->d_mhscale, n * sizeof(float)));

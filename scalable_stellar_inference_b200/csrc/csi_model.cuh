@@ -30,6 +30,7 @@ enum Slot { S_TAU = 0, S_EVOL = 1, S_MASS = 2, S_MH = 3, S_Y = 4, S_A = 5, S_PY 
 enum PriorMode { P_FLAT = 0, P_INFORMATIVE = 1, P_HIER = 2 };
 
 constexpr float kLn10 = 2.302585092994046f;
+constexpr float kLog2_10 = 3.321928094887362f;  // |argument| < 2 where it is used: 10^v = 2^(v log2 10) to ~1 ulp
 constexpr float kHalfLog2Pi = 0.9189385332046727f;
 constexpr float kInvSqrt2 = 0.7071067811865476f;
 
@@ -39,6 +40,8 @@ enum TnKind { TN_REAL = 0, TN_LOWER = 1, TN_UPPER = 2, TN_INTERVAL = 3 };
 struct TnC {            // TruncatedNormal with constant bounds (loc/scale may be overridden per star)
   float loc, scale, low, high;
   float logz;           // log(Phi(beta) - Phi(alpha)) for the constant loc/scale (host, fp64)
+  float inv_scale;      // 1 / scale and
+  float lognorm;        // logz + log(scale), both formed in fp64 on the host: no per-star divide / logf for them
   float logw;           // log(high - low) for the interval transform
   int kind;
 };
@@ -67,7 +70,7 @@ struct StarIO {
   const float *diag[kMaxObs];   // entries may be null (= 0)
   const float *obsm[kMaxMean];  // the same columns indexed by the MEAN they observe (null = unobserved); kind diag
   const float *diagm[kMaxMean];
-  const float *mh_loc, *mh_scale, *mh_logz;  // null = constants of DevModel::mh
+  const float *mh_loc, *mh_scale, *mh_logz;  // per-star M_H prior: loc, 1 / scale, logz + log(scale); null = DevModel::mh
   const float *z_hyper;         // 5 values (hierarchical only)
   long long n;
 };
@@ -96,6 +99,16 @@ CSI_DEV float sigmoidf_(float u) { return 1.0f / (1.0f + expf(-u)); }
 CSI_DEV float log_sigmoid_prod(float u) {
   float a = fabsf(u);
   return -a - 2.0f * log1pf(expf(-a));
+}
+
+// sigmoid(u) together with l1 = log(1 + exp(-|u|)) from ONE exponential:
+//   log(s (1 - s)) = -|u| - 2 l1,   log s = min(u, 0) - l1,   log(1 - s) = -max(u, 0) - l1
+CSI_DEV void sig_pair(float u, float &s, float &l1) {
+  const float a = fabsf(u);
+  const float e = expf(-a);
+  const float inv = 1.0f / (1.0f + e);
+  s = (u >= 0.0f) ? inv : e * inv;
+  l1 = log1pf(e);
 }
 
 // log Phi(x), x <= 0 branch uses the scaled complementary error function (no underflow)
@@ -129,11 +142,12 @@ CSI_DEV void log_ndtr_diff(float alpha, float beta, float &logz, float &ra, floa
 // numpyro biject_to: value, dvalue/du, log|J|, dlog|J|/du
 CSI_DEV void bounded_transform(const TnC &c, float u, float &v, float &dv, float &ld, float &dld) {
   if (c.kind == TN_INTERVAL) {
-    float s = sigmoidf_(u);
+    float s, l1;
+    sig_pair(u, s, l1);
     float w = c.high - c.low;
     v = c.low + w * s;
     dv = w * s * (1.0f - s);
-    ld = c.logw + log_sigmoid_prod(u);
+    ld = c.logw - fabsf(u) - 2.0f * l1;
     dld = 1.0f - 2.0f * s;
   } else if (c.kind == TN_UPPER) {
     float e = expf(u);
@@ -148,13 +162,14 @@ CSI_DEV void bounded_transform(const TnC &c, float u, float &v, float &dv, float
 
 // constant-bound TruncatedNormal site in unconstrained space: value, dv/du, log-term, dlog-term/du.
 // loc / scale / logz may be per-star overrides (the M_H prior of scripts/model_star.py:126-128).
-CSI_DEV void tn_site(const TnC &c, float u, float loc, float scale, float logz, float &v, float &dv,
+// inv_scale = 1 / scale, lognorm = logz + log(scale) (TnC::inv_scale / lognorm or the per-star arrays)
+CSI_DEV void tn_site(const TnC &c, float u, float loc, float inv_scale, float lognorm, float &v, float &dv,
                      float &lt, float &dlt) {
   float ld, dld;
   bounded_transform(c, u, v, dv, ld, dld);
-  float r = (v - loc) / scale;
-  lt = -0.5f * r * r - logf(scale) - kHalfLog2Pi - logz + ld;
-  dlt = -r / scale * dv + dld;
+  float r = (v - loc) * inv_scale;
+  lt = -0.5f * r * r - kHalfLog2Pi - lognorm + ld;
+  dlt = -r * inv_scale * dv + dld;
 }
 
 // log TN(x; mu, sigma, low, high) and partials wrt x, mu, sigma (finite bounds)
@@ -214,13 +229,13 @@ CSI_DEV void hyper_eval(const DevModel &m, const float *zh, HyperVals &h) {
   lp += -0.5f * r * r - logf(m.y0_scale) - kHalfLog2Pi;
   h.gprior[0] = -r / m.y0_scale;
   float lt, dlt;
-  tn_site(m.dydz, zh[1], m.dydz.loc, m.dydz.scale, m.dydz.logz, h.dydz, h.ddydz, lt, dlt);
+  tn_site(m.dydz, zh[1], m.dydz.loc, m.dydz.inv_scale, m.dydz.lognorm, h.dydz, h.ddydz, lt, dlt);
   lp += lt; h.gprior[1] = dlt;
   float py;
   gamma_site(zh[2], m.py_conc, m.py_rate, m.py_const, py, lt, dlt);
   lp += lt; h.gprior[2] = dlt;
   h.sigma_y = rsqrtf(py);
-  tn_site(m.mu_a, zh[3], m.mu_a.loc, m.mu_a.scale, m.mu_a.logz, h.mu_a, h.dmu_a, lt, dlt);
+  tn_site(m.mu_a, zh[3], m.mu_a.loc, m.mu_a.inv_scale, m.mu_a.lognorm, h.mu_a, h.dmu_a, lt, dlt);
   lp += lt; h.gprior[3] = dlt;
   float pa;
   gamma_site(zh[4], m.pa_conc, m.pa_rate, m.pa_const, pa, lt, dlt);
@@ -264,8 +279,8 @@ CSI_DEV void star_load_z(const DevModel &m, const StarIO &io, long long i, StarI
 #pragma unroll
   for (int s = 0; s < kSlots; ++s) in.zv[s] = io.z[s] ? io.z[s][i] : 0.0f;
   in.mloc = io.mh_loc ? io.mh_loc[i] : m.mh.loc;
-  in.mscale = io.mh_scale ? io.mh_scale[i] : m.mh.scale;
-  in.mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.logz;
+  in.mscale = io.mh_scale ? io.mh_scale[i] : m.mh.inv_scale;
+  in.mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.lognorm;
 }
 
 CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, StarState &st, HyperAcc &acc) {
@@ -280,20 +295,20 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
   lp += lt; st.gp[S_TAU] = dlt;
   // log_evol, log_mass, M_H: constant-bound truncated normals (:149-161 / :304-316)
   float v, dv;
-  tn_site(m.log_evol, zv[S_EVOL], m.log_evol.loc, m.log_evol.scale, m.log_evol.logz, v, dv, lt, dlt);
+  tn_site(m.log_evol, zv[S_EVOL], m.log_evol.loc, m.log_evol.inv_scale, m.log_evol.lognorm, v, dv, lt, dlt);
   lp += lt; st.gp[S_EVOL] = dlt;
-  float evol = exp10f(v);
+  float evol = exp2f(v * kLog2_10);
   st.x[0] = evol; st.c_evol = kLn10 * evol * dv;
-  tn_site(m.log_mass, zv[S_MASS], m.log_mass.loc, m.log_mass.scale, m.log_mass.logz, v, dv, lt, dlt);
+  tn_site(m.log_mass, zv[S_MASS], m.log_mass.loc, m.log_mass.inv_scale, m.log_mass.lognorm, v, dv, lt, dlt);
   lp += lt; st.gp[S_MASS] = dlt;
-  float mass = exp10f(v);
+  float mass = exp2f(v * kLog2_10);
   st.log_mass = v; st.x[1] = mass; st.c_mass = kLn10 * mass * dv; st.dlm = dv;
   float mh;
   tn_site(m.mh, zv[S_MH], mloc, mscale, mlogz, mh, dv, lt, dlt);
   lp += lt; st.gp[S_MH] = dlt;
   st.x[2] = mh; st.dmh = dv;
 
-  float t = exp10f(-(mh + m.log_zx_sun));
+  float t = exp2f(-(mh + m.log_zx_sun) * kLog2_10);
   float q = 1.0f / (1.0f + t);
   float dq_dmh = kLn10 * q * (1.0f - q);
   float g_mh_prior = 0.0f;
@@ -306,12 +321,13 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
     float dmu_dy0 = inv1f;
     float dmu_df = (1.0f - h.y0) * inv1f * inv1f;
     float uy = zv[S_Y];
-    float sy = sigmoidf_(uy);
+    float sy, l1y;
+    sig_pair(uy, sy, l1y);
     float y = m.y_lo + m.y_w * sy;
     float dy = m.y_w * sy * (1.0f - sy);
     float lpy, dl_dy, dl_dmu, dl_dsig;
     tn_logpdf_grads_pre(y, mu_y, h.y_inv, h.y_logsig, m.y_lo, m.y_hi, lpy, dl_dy, dl_dmu, dl_dsig);
-    lp += lpy + m.log_y_w + log_sigmoid_prod(uy);
+    lp += lpy + m.log_y_w - fabsf(uy) - 2.0f * l1y;
     st.gp[S_Y] = dl_dy * dy + (1.0f - 2.0f * sy);
     g_mh_prior += dl_dmu * dmu_df * h.dydz * dq_dmh;
     acc.g[0] += (double)(dl_dmu * dmu_dy0);
@@ -319,7 +335,8 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
     acc.g[2] += (double)dl_dsig;
     st.x[3] = y; st.dy = dy;
     float ua = zv[S_A];
-    float sa = sigmoidf_(ua);
+    float sa, l1a;
+    sig_pair(ua, sa, l1a);
     float a = m.a_lo + m.a_w * sa;
     float da = m.a_w * sa * (1.0f - sa);
     // TN(mu_a, sigma_a) has the same normaliser for every star: evaluated once in hyper_eval
@@ -328,7 +345,7 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
     const float dl_da = -ra_ * h.a_inv;
     const float dl_dmua = ra_ * h.a_inv + (h.a_rb - h.a_ra) * h.a_inv;
     const float dl_dsiga = (ra_ * ra_ - 1.0f) * h.a_inv + (h.a_beta * h.a_rb - h.a_alpha * h.a_ra) * h.a_inv;
-    lp += lpa + m.log_a_w + log_sigmoid_prod(ua);
+    lp += lpa + m.log_a_w - fabsf(ua) - 2.0f * l1a;
     st.gp[S_A] = dl_da * da + (1.0f - 2.0f * sa);
     acc.g[3] += (double)dl_dmua;
     acc.g[4] += (double)dl_dsiga;
@@ -388,8 +405,10 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
   if (m.bands > 0) {
     // scaled_distance ~ Beta(c1, c0) on (0,1), sigmoid transform (notebook/single-star-phot.ipynb cell [7])
     float u = zv[S_SD];
-    float sd = sigmoidf_(u);
-    lp += m.sd_const + (m.sd_c1 - 1.0f) * logf(sd) + (m.sd_c0 - 1.0f) * log1pf(-sd) + log_sigmoid_prod(u);
+    float sd, l1;
+    sig_pair(u, sd, l1);
+    const float log_sd = fminf(u, 0.0f) - l1, log_1msd = -fmaxf(u, 0.0f) - l1;  // log s, log(1 - s)
+    lp += m.sd_const + (m.sd_c1 - 1.0f) * log_sd + (m.sd_c0 - 1.0f) * log_1msd + (log_sd + log_1msd);
     st.gp[S_SD] = m.sd_c1 * (1.0f - sd) - m.sd_c0 * sd;
     st.dist = m.max_distance * sd;
     st.dsd = m.max_distance * sd * (1.0f - sd);

@@ -78,7 +78,8 @@ constexpr int oOutLoc = oInScale + 8;   // [4]
 constexpr int oOutScale = oOutLoc + 4;  // [4]
 constexpr int oGain = oOutScale + 4;    // [8] s_w * (largest row L1 norm) of the B image of stages 7..12
 constexpr int oBiasA = oGain + 8;       // [1] constant A entry of the bias products (+3 pad)
-constexpr int kSmallFloats = oBiasA + 4;
+constexpr int oInInv = oBiasA + 4;      // [8] 1 / in_scale (fp64 reciprocal, rounded once)
+constexpr int kSmallFloats = oInInv + 8;
 
 struct __align__(128) Smem {
   uint8_t wring[2][2][2 * kHalfBytes];  // weight slots: [tile][K-half][hi half | lo half]
@@ -476,11 +477,11 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         st = StarState{};
         st.x[0] = 0.3f; st.x[1] = 1.1f; st.x[2] = 0.1f; st.x[3] = 0.27f; st.x[4] = 2.0f; st.tau = 1.0f; st.dist = 100.f;
 #pragma unroll
-        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) / sm[oInScale + k] * kActScale;
+        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else if (valid) {
         star_pre(m, hv, io, i, st, acc);
 #pragma unroll
-        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) / sm[oInScale + k] * kActScale;
+        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else {
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = 0.0f;
@@ -587,7 +588,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
           if (valid) {
             float g_x[5];
 #pragma unroll
-            for (int k = 0; k < 5; ++k) g_x[k] = __uint_as_float(r8[k]) * un / sm[oInScale + k];
+            for (int k = 0; k < 5; ++k) g_x[k] = __uint_as_float(r8[k]) * un * sm[oInInv + k];
             star_post(m, io, i, st, g_x);
             acc.lp += (double)st.lp;
           }
@@ -749,6 +750,7 @@ void tc_build_images(const csi_net &net, uint8_t *img, uint8_t *res, float *smal
   for (int k = 0; k < 5; ++k) {
     small[oInLoc + k] = (float)net.in_loc[k];
     small[oInScale + k] = (float)net.in_scale[k];
+    small[oInInv + k] = (float)(1.0 / net.in_scale[k]);
   }
 }
 
