@@ -1,0 +1,323 @@
+"""Star-sharded No-U-Turn sampler: the caller of the hot path (numpyro's role in the reference).
+
+The reference drives its models with ``numpyro.infer.NUTS`` / ``MCMC`` (scripts/model_star.py:132-155) using
+``init_to_median``, ``target_accept_prob=0.8``, ``find_heuristic_step_size=True``, a regularised DIAGONAL mass
+matrix and ``max_tree_depth=10`` (scripts/model_star.py:18-22).  numpyro is third-party and absent here, so this
+module restates the same algorithm (multinomial NUTS with the generalised U-turn criterion, dual-averaging step
+size, Stan-style windowed variance adaptation -- Hoffman & Gelman 2014, Betancourt 2017) around ONE primitive:
+
+    potential(z) -> (U, dU/dz)      one evaluation of the hot path (libcsi on the GPU, the oracle in the CPU tests)
+
+Vectors are torch tensors (CPU or CUDA: PyTorch is plumbing here).  With the star axis sharded over ranks a vector
+is ``[hyper (replicated) | local stars]``: inner products add the hyper part once and SUM-allreduce the star part,
+momenta of the hyper sites and every accept / direction decision come from a generator seeded identically on all
+ranks, so that every rank builds the same tree.  Energies are kept in float64 (|U| ~ 1e7 at 1 M stars).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+
+class VectorSpace:
+    """Inner products of ``[hyper | local stars]`` vectors; ``group`` = torch.distributed group or None."""
+
+    def __init__(self, n_hyper: int = 0, group=None, sharded: bool = False):
+        self.n_hyper, self.group, self.sharded = n_hyper, group, sharded
+
+    def dots(self, pairs):
+        """Several inner products with ONE collective: returns a list of python floats."""
+        nh = self.n_hyper
+        loc = torch.stack([torch.dot(a[nh:].double(), b[nh:].double()) for a, b in pairs])
+        if self.sharded:
+            import torch.distributed as dist
+            dist.all_reduce(loc, group=self.group)
+        if nh:
+            loc = loc + torch.stack([torch.dot(a[:nh].double(), b[:nh].double()) for a, b in pairs])
+        return loc.tolist()
+
+
+@dataclass
+class _Tree:
+    z_left: torch.Tensor
+    r_left: torch.Tensor
+    g_left: torch.Tensor
+    z_right: torch.Tensor
+    r_right: torch.Tensor
+    g_right: torch.Tensor
+    z_prop: torch.Tensor
+    u_prop: float
+    g_prop: torch.Tensor
+    log_w: float            # log of the summed multinomial weights exp(-H)
+    r_sum: torch.Tensor
+    turning: bool
+    diverging: bool
+    sum_accept: float
+    n_prop: int
+
+
+def _logaddexp(a, b):
+    m = max(a, b)
+    return m if m == -math.inf else m + math.log(math.exp(a - m) + math.exp(b - m))
+
+
+class NUTS:
+    """One chain.  ``potential(z) -> (U: float, grad: tensor)`` must return a tensor it will not overwrite."""
+
+    def __init__(self, potential, space: VectorSpace | None = None, target_accept: float = 0.8,
+                 max_tree_depth: int = 10, seed: int = 0, rank: int = 0, adapt_mass: bool = True,
+                 max_delta_energy: float = 1000.0):
+        self.potential, self.space = potential, space or VectorSpace()
+        self.target, self.max_depth, self.max_de = target_accept, max_tree_depth, max_delta_energy
+        self.adapt_mass = adapt_mass
+        self.rng = np.random.default_rng(seed)                    # shared decisions: same seed on every rank
+        self.seed, self.rank = seed, rank
+        self.gen_shared = self.gen_local = None
+        self.n_evals = 0
+
+    # ---- primitives ------------------------------------------------------------------------------------------
+    def _pot(self, z):
+        self.n_evals += 1
+        return self.potential(z)
+
+    def _momentum(self, like):
+        nh = self.space.n_hyper
+        if self.gen_shared is None:
+            self.gen_shared = torch.Generator(device=like.device).manual_seed(1234567 + self.seed)
+            self.gen_local = torch.Generator(device=like.device).manual_seed(7654321 + 1000 * self.seed + self.rank)
+        r = torch.empty_like(like)
+        if nh:
+            r[:nh] = torch.randn(nh, generator=self.gen_shared, device=like.device, dtype=like.dtype)
+        r[nh:] = torch.randn(like.numel() - nh, generator=self.gen_local, device=like.device, dtype=like.dtype)
+        return r * self.inv_mass.rsqrt()                          # r ~ N(0, M), M = 1 / inv_mass
+
+    def _kinetic(self, r):
+        return 0.5 * self.space.dots([(r, self.inv_mass * r)])[0]
+
+    def _leapfrog(self, z, r, g, eps):
+        r = r - (0.5 * eps) * g
+        z = z + eps * (self.inv_mass * r)
+        u, g = self._pot(z)
+        r = r - (0.5 * eps) * g
+        return z, r, u, g
+
+    def _is_turning(self, r_left, r_right, r_sum):
+        # numpyro / Stan generalised criterion on the summed momentum (end points counted half)
+        rc = r_sum - 0.5 * (r_left + r_right)
+        a, b = self.space.dots([(self.inv_mass * r_left, rc), (self.inv_mass * r_right, rc)])
+        return a <= 0.0 or b <= 0.0
+
+    # ---- tree ------------------------------------------------------------------------------------------------
+    def _base(self, z, r, g, eps, h0):
+        z1, r1, u1, g1 = self._leapfrog(z, r, g, eps)
+        h1 = u1 + self._kinetic(r1)
+        de = h1 - h0
+        if not math.isfinite(de):
+            de = math.inf
+        return _Tree(z1, r1, g1, z1, r1, g1, z1, u1, g1, -de, r1, False, de > self.max_de,
+                     min(1.0, math.exp(-de)) if de < math.inf else 0.0, 1)
+
+    def _combine(self, cur: _Tree, new: _Tree, going_right: bool, biased: bool):
+        log_w = _logaddexp(cur.log_w, new.log_w)
+        p = math.exp(min(0.0, new.log_w - cur.log_w)) if biased else math.exp(new.log_w - log_w)
+        if new.turning or new.diverging:
+            p = 0.0  # no proposal is taken from a sub-tree that turned or diverged
+        take = self.rng.random() < p
+        left, right = (cur, new) if going_right else (new, cur)
+        r_sum = cur.r_sum + new.r_sum
+        src = new if take else cur
+        return _Tree(left.z_left, left.r_left, left.g_left, right.z_right, right.r_right, right.g_right,
+                     src.z_prop, src.u_prop, src.g_prop, log_w, r_sum, False, False,
+                     cur.sum_accept + new.sum_accept, cur.n_prop + new.n_prop)
+
+    def _build(self, z, r, g, eps, depth, h0):
+        if depth == 0:
+            return self._base(z, r, g, eps, h0)
+        half = self._build(z, r, g, eps, depth - 1, h0)
+        if half.turning or half.diverging:
+            return half
+        going_right = eps > 0
+        if going_right:
+            other = self._build(half.z_right, half.r_right, half.g_right, eps, depth - 1, h0)
+        else:
+            other = self._build(half.z_left, half.r_left, half.g_left, eps, depth - 1, h0)
+        tree = self._combine(half, other, going_right, biased=False)
+        tree.diverging = other.diverging
+        tree.turning = other.turning or (not other.diverging and self._is_turning(tree.r_left, tree.r_right, tree.r_sum))
+        return tree
+
+    def transition(self, z, u, g, step_size):
+        r0 = self._momentum(z)
+        h0 = u + self._kinetic(r0)
+        tree = _Tree(z, r0, g, z, r0, g, z, u, g, 0.0, r0, False, False, 0.0, 0)
+        depth, diverging = 0, False
+        while depth < self.max_depth:
+            going_right = self.rng.random() < 0.5
+            if going_right:
+                new = self._build(tree.z_right, tree.r_right, tree.g_right, step_size, depth, h0)
+            else:
+                new = self._build(tree.z_left, tree.r_left, tree.g_left, -step_size, depth, h0)
+            depth += 1
+            if new.turning or new.diverging:
+                tree.sum_accept += new.sum_accept
+                tree.n_prop += new.n_prop
+                diverging = new.diverging
+                break
+            tree = self._combine(tree, new, going_right, biased=True)
+            if self._is_turning(tree.r_left, tree.r_right, tree.r_sum):
+                break
+        accept = tree.sum_accept / max(tree.n_prop, 1)
+        return tree.z_prop, tree.u_prop, tree.g_prop, accept, depth, diverging
+
+    # ---- step size and mass matrix adaptation -------------------------------------------------------------------
+    def find_heuristic_step_size(self, z, u, g, step_size=1.0):
+        """Double / halve the step until the one-step acceptance probability crosses the target (numpyro
+        ``find_reasonable_step_size``)."""
+        log_target = math.log(self.target)
+        direction = 0
+        for _ in range(60):
+            r = self._momentum(z)
+            h0 = u + self._kinetic(r)
+            _, r1, u1, _ = self._leapfrog(z, r, g, step_size)
+            de = (u1 + self._kinetic(r1)) - h0
+            new_dir = 1 if (math.isfinite(de) and -de > log_target) else -1
+            if direction and new_dir != direction:
+                break
+            direction = new_dir
+            step_size *= 2.0 ** direction
+            if not (1e-10 < step_size < 1e10):
+                break
+        return step_size
+
+    @staticmethod
+    def adaptation_windows(num_warmup):
+        """(start, end) of the slow (mass-matrix) windows, Stan / numpyro schedule."""
+        if num_warmup < 20:
+            return []
+        init, term, base = 75, 50, 25
+        if init + base + term > num_warmup:
+            init, term = int(0.15 * num_warmup), int(0.1 * num_warmup)
+            base = num_warmup - init - term
+        wins, start, size = [], init, base
+        end_slow = num_warmup - term
+        while start < end_slow:
+            end = start + size
+            if end + 2 * size > end_slow:
+                end = end_slow
+            wins.append((start, end))
+            start, size = end, 2 * size
+        return wins
+
+    def run(self, z0, num_warmup, num_samples, collect=None, progress=None):
+        """Returns dict(samples=[collect(z) per draw], accept, depth, diverging, step_size, n_evals, potential).
+        ``collect`` maps the state vector to what is kept (default: the first ``n_hyper`` entries, on the host)."""
+        nh = self.space.n_hyper
+        collect = collect or (lambda z: z[:max(nh, 1)].detach().double().cpu().numpy().copy())
+        z = z0.clone()
+        self.inv_mass = torch.ones_like(z)
+        u, g = self._pot(z)
+        if not math.isfinite(u):
+            raise ValueError("non-finite potential at the initial point")
+        step = self.find_heuristic_step_size(z, u, g)
+        # dual averaging (Nesterov / Hoffman-Gelman): log step
+        t0, kappa, gamma = 10.0, 0.75, 0.05
+        da = dict(mu=math.log(10.0 * step), x_bar=0.0, h_bar=0.0, t=0)
+        windows = self.adaptation_windows(num_warmup) if self.adapt_mass else []
+        ends = {e: s for s, e in windows}
+        in_window = lambda i: any(s <= i < e for s, e in windows)  # noqa: E731
+        w_n, w_mean, w_m2 = 0, torch.zeros_like(z, dtype=torch.float64), torch.zeros_like(z, dtype=torch.float64)
+        out = dict(samples=[], accept=[], depth=[], diverging=[], potential=[])
+        for it in range(num_warmup + num_samples):
+            warm = it < num_warmup
+            z, u, g, acc, depth, div = self.transition(z, u, g, step)
+            if warm:
+                da["t"] += 1
+                t = da["t"]
+                da["h_bar"] = (1 - 1 / (t + t0)) * da["h_bar"] + (self.target - acc) / (t + t0)
+                x = da["mu"] - math.sqrt(t) / gamma * da["h_bar"]
+                eta = t ** (-kappa)
+                da["x_bar"] = eta * x + (1 - eta) * da["x_bar"]
+                step = math.exp(x)
+                if in_window(it):
+                    w_n += 1
+                    d = z.double() - w_mean
+                    w_mean += d / w_n
+                    w_m2 += d * (z.double() - w_mean)
+                if (it + 1) in ends and w_n > 1:
+                    var = w_m2 / (w_n - 1)
+                    var = var * (w_n / (w_n + 5.0)) + 1e-3 * (5.0 / (w_n + 5.0))      # Stan's regularisation
+                    self.inv_mass = var.to(z.dtype)
+                    w_n = 0; w_mean.zero_(); w_m2.zero_()
+                    step = self.find_heuristic_step_size(z, u, g, math.exp(da["x_bar"]))
+                    da = dict(mu=math.log(10.0 * step), x_bar=0.0, h_bar=0.0, t=0)
+                if it + 1 == num_warmup:
+                    step = math.exp(da["x_bar"]) if da["t"] > 0 else step
+                    self.n_evals_warmup = self.n_evals
+            else:
+                out["samples"].append(collect(z))
+                out["accept"].append(acc); out["depth"].append(depth); out["diverging"].append(div)
+                out["potential"].append(u)
+            if progress:
+                progress(it, warm, step, depth, acc)
+        out.update(step_size=step, n_evals=self.n_evals, z_last=z)
+        return out
+
+
+def effective_sample_size(x):
+    """Bulk ESS of draws x[chain, draw] (Geyer initial monotone sequence on split chains; the estimator of
+    numpyro.diagnostics.effective_sample_size / Stan)."""
+    x = np.asarray(x, dtype=np.float64)
+    if x.ndim == 1:
+        x = x[None]
+    half = x.shape[1] // 2
+    x = np.concatenate([x[:, :half], x[:, half:2 * half]], axis=0)      # split chains
+    m, n = x.shape
+    xc = x - x.mean(axis=1, keepdims=True)
+    nfft = 1 << int(np.ceil(np.log2(2 * n)))
+    f = np.fft.rfft(xc, nfft, axis=1)
+    acov = np.fft.irfft(f * np.conj(f), nfft, axis=1)[:, :n] / n
+    var_within = acov[:, 0].mean() * n / (n - 1.0)
+    var_plus = acov[:, 0].mean() + (x.mean(axis=1).var(ddof=1) if m > 1 else 0.0)
+    if var_plus <= 0:
+        return float(m * n)
+    rho = 1.0 - (var_within - acov.mean(axis=0) * n / (n - 1.0)) / var_plus
+    rho[0] = 1.0
+    pairs = rho[: 2 * (n // 2)].reshape(-1, 2).sum(axis=1)             # P_k = rho_2k + rho_2k+1
+    pos = np.where(pairs < 0)[0]
+    k = pos[0] if len(pos) else len(pairs)
+    pk = np.minimum.accumulate(pairs[:k]) if k > 0 else np.array([1.0])
+    tau = -1.0 + 2.0 * pk.sum()
+    return float(m * n / max(tau, 1.0 / math.log10(max(m * n, 10))))
+
+
+class DevicePotential:
+    """``potential(z)`` on the B200 path: z is a float32 CUDA tensor in ``csi_layout`` order ([hyper | local stars]).
+    One libcsi launch + (sharded) one 6-double allreduce; the summed hyper-gradient replaces the local partials."""
+
+    def __init__(self, model, group=None):
+        from .parallel import ShardedPotential
+        self.sp = ShardedPotential(model, group)
+        self.model, self.nh = model, len(model.hyper_sites)
+
+    def __call__(self, z):
+        sp = self.sp
+        out, grad = sp.value_and_grad_device(z.contiguous())
+        g = grad.clone()
+        if self.nh:
+            g[: self.nh] = out[1: 1 + self.nh].to(g.dtype)
+        return float(out[0].item()), g
+
+
+def sample_model(model, z0_flat, num_warmup, num_samples, seed=0, group=None, rank=0, world=1, collect=None, **kw):
+    """NUTS over a conditioned (and, for world > 1, sharded) model; returns the run dict with hyper-site draws."""
+    dev = torch.device("cuda", model.device)
+    pot = DevicePotential(model, group)
+    space = VectorSpace(n_hyper=pot.nh, group=group, sharded=world > 1)
+    nuts = NUTS(pot, space, seed=seed, rank=rank, **kw)
+    z0 = torch.as_tensor(np.asarray(z0_flat, dtype=np.float32), device=dev)
+    out = nuts.run(z0, num_warmup, num_samples, collect=collect)
+    out["n_evals_warmup"] = getattr(nuts, "n_evals_warmup", 0)
+    return out

@@ -1,0 +1,92 @@
+"""NUTS driver (the caller of the hot path; numpyro's role, scripts/model_star.py:132-155): CPU checks of the
+sampler itself, and on the GPU posterior agreement between the CUDA potential and the oracle potential."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+import parity_util as PU
+from oracle import model as M
+from scalable_stellar_inference_b200.nuts import NUTS, VectorSpace, effective_sample_size
+
+
+def test_adaptation_windows_follow_stan_schedule():
+    assert NUTS.adaptation_windows(1000) == [(75, 100), (100, 150), (150, 250), (250, 450), (450, 950)]
+    assert NUTS.adaptation_windows(10) == []
+    w = NUTS.adaptation_windows(100)           # 15 % / 75 % / 10 % rule
+    assert w[0][0] == 15 and w[-1][1] == 90
+
+
+def test_gaussian_moments_and_ess():
+    d = 12
+    sig = torch.linspace(0.2, 2.5, d, dtype=torch.float64)
+
+    def pot(z):
+        return float(0.5 * (z ** 2 / sig ** 2).sum()), z / sig ** 2
+
+    out = NUTS(pot, VectorSpace(), seed=3).run(torch.full((d,), 0.3, dtype=torch.float64), 300, 800,
+                                                 collect=lambda z: z.numpy().copy())
+    s = np.array(out["samples"])
+    ess = np.array([effective_sample_size(s[:, k]) for k in range(d)])
+    assert np.all(np.abs(s.mean(0)) < 5 * sig.numpy() / np.sqrt(ess))
+    assert np.all(np.abs(s.std(0) / sig.numpy() - 1) < 0.15)
+    assert sum(out["diverging"]) == 0 and 0.7 < np.mean(out["accept"]) <= 1.0
+
+
+def test_ess_of_independent_and_correlated_draws():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(4000)
+    assert 3000 < effective_sample_size(x) < 5500
+    y = np.zeros(4000)
+    for i in range(1, 4000):                    # AR(1), rho = 0.9 -> ESS ~ n (1 - rho) / (1 + rho) ~ 210
+        y[i] = 0.9 * y[i - 1] + rng.standard_normal()
+    assert 100 < effective_sample_size(y) < 450
+
+
+def test_sharded_inner_products_match_unsharded():
+    # [hyper | stars] split over two "ranks" by hand: hyper counted once, star parts summed
+    rng = np.random.default_rng(1)
+    nh, n = 3, 10
+    a, b = torch.tensor(rng.standard_normal(nh + n)), torch.tensor(rng.standard_normal(nh + n))
+    full = VectorSpace(nh).dots([(a, b)])[0]
+    parts = 0.0
+    for lo, hi in ((0, 4), (4, 10)):
+        sl = torch.cat([a[:nh], a[nh + lo: nh + hi]]), torch.cat([b[:nh], b[nh + lo: nh + hi]])
+        parts += VectorSpace(0).dots([(sl[0][nh:], sl[1][nh:])])[0]
+    parts += float(torch.dot(a[:nh], b[:nh]))
+    assert math.isclose(full, parts, rel_tol=1e-12)
+
+
+@pytest.mark.gpu
+def test_posterior_of_cuda_potential_matches_oracle_potential():
+    """Posterior means / spreads of every site: NUTS over libcsi vs the same NUTS over the fp64 oracle on the same
+    4 synthetic stars (MultiStarModel, informative prior); agreement within Monte-Carlo standard error
+    (north_star's posterior criterion).  The hierarchical posterior needs tree depth 9-10 at this size -- minutes of
+    oracle time -- so the cheap well-conditioned model carries this test."""
+    from scalable_stellar_inference_b200.nuts import sample_model
+    name, n = "multi_informative", 4
+    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, n)
+    model = PU.product_model(name, n, "tcgen05").condition(obs, diag, M_H_loc=ml, M_H_scale=ms)
+    zf = model.flatten(z0)
+    nw, ns = 150, 250
+    keep = lambda z: z.detach().double().cpu().numpy().copy()  # noqa: E731
+    out_gpu = sample_model(model, zf, nw, ns, seed=5, collect=keep)
+
+    def oracle_pot(z):
+        zd = model.unflatten(z.numpy().astype(np.float32))
+        u, g = M.potential_and_grad(spec, zd, obs, diag, ml, ms)
+        return float(u), torch.as_tensor(model.flatten(g).astype(np.float64))
+
+    out_cpu = NUTS(oracle_pot, VectorSpace(len(model.hyper_sites)), seed=6).run(
+        torch.as_tensor(zf.astype(np.float64)), nw, ns, collect=keep)
+    a, b = np.array(out_gpu["samples"]), np.array(out_cpu["samples"])
+    bad = 0
+    for k in range(a.shape[1]):
+        ea, eb = effective_sample_size(a[:, k]), effective_sample_size(b[:, k])
+        mcse = math.sqrt(a[:, k].var() / ea + b[:, k].var() / eb)
+        bad += abs(a[:, k].mean() - b[:, k].mean()) > 4.0 * mcse
+        assert abs(a[:, k].mean() - b[:, k].mean()) < 6.0 * mcse, (k, a[:, k].mean(), b[:, k].mean(), mcse)
+        assert 0.4 < a[:, k].std() / b[:, k].std() < 2.5
+    assert bad <= 1
+    assert sum(out_gpu["diverging"]) <= 0.1 * ns
