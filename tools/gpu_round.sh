@@ -14,7 +14,7 @@ CSI_TC_DEBUG=8 timeout 300 python tools/trace_tc.py > gpurun_out/trace.txt 2>&1
 if [ "$1" == "ncu" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv \
   python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:potential_tc_kernel -s 5 -c 1 \
-  -o gpurun_out/prof -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:potential_tc_kernel -s 16 -c 1 \
+  -o gpurun_out/prof_pot -f python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 fi
 ls -la gpurun_out
