@@ -30,6 +30,32 @@ def shard_problem(z: dict, obs, diag, mh_loc, mh_scale, rank: int, world: int):
     return zl, np.asarray(obs)[sl], f(diag), f(mh_loc), f(mh_scale)
 
 
+def block_bounds(lo: int, hi: int, n_blocks: int, unit: int):
+    """Cut stars [lo, hi) into <= n_blocks contiguous blocks whose sizes are whole multiples of ``unit`` (one full
+    round of the persistent kernel: SMs x 2 tiles x 128 stars), remainder last, so that no block pays for a
+    partly filled round."""
+    n = hi - lo
+    units = max(1, -(-n // unit))
+    nb = max(1, min(n_blocks, units))
+    base, rem = divmod(units, nb)
+    out, pos = [], lo
+    for b in range(nb):
+        size = (base + (1 if b < rem else 0)) * unit
+        end = min(hi, pos + size)
+        if end > pos:
+            out.append((pos, end))
+        pos = end
+    return out
+
+
+def slice_problem(z: dict, obs, diag, mh_loc, mh_scale, lo: int, hi: int):
+    """Stars [lo, hi) of a full problem; hyper sites are replicated."""
+    sl = slice(lo, hi)
+    zl = {k: (v if np.ndim(v) == 0 else np.asarray(v)[sl]) for k, v in z.items()}
+    f = lambda a: None if a is None else (a if np.ndim(a) == 0 else np.asarray(a)[sl])  # noqa: E731
+    return zl, np.asarray(obs)[sl], f(diag), f(mh_loc), f(mh_scale)
+
+
 def allreduce_out(out, group=None):
     """SUM-allreduce of the 6-double vector [U, dU/dhyper]; a no-op without an initialised process group."""
     import torch.distributed as dist
@@ -82,3 +108,71 @@ class ShardedPotential:
         self.out_pin.copy_(self.out_dev, non_blocking=True)
         torch.cuda.current_stream(self.device).synchronize()
         return float(self.out_pin[0]), self.out_pin[1:6].numpy(), self.grad_pin.numpy()
+
+
+class PipelinedHostPotential:
+    """End-to-end evaluation through HOST buffers with the copies hidden behind the kernel.
+
+    The local stars are cut into ``len(models)`` contiguous blocks, each with its own libcsi handle, device
+    buffers, pinned host buffers and CUDA stream.  One evaluation issues, per block, H2D of the block's z -> the
+    block's kernel -> D2H of its gradient and 6 sums; the copy engines and the SMs serve different blocks at the same
+    time, so a step costs ~max(PCIe time, kernel time) instead of their sum.  The host-side layout is
+    block-major -- ``z_views[b][site]`` / ``grad_views[b][site]`` are numpy views into the pinned buffers that a
+    host-side sampler reads and writes in place (the hyper sites are replicated into every block by
+    ``set_hyper``).  ``models[b]`` must be conditioned on block b and sharded as ``set_shard(rank * B + b, world * B)``
+    so that the hyper-prior terms are counted once.
+    """
+
+    def __init__(self, models, group=None):
+        import torch
+        self.torch, self.models, self.group = torch, list(models), group
+        self.device = torch.device("cuda", models[0].device)
+        self.n_hyper = len(models[0].hyper_sites)
+        self.blocks = []
+        self.h2d_bytes = self.d2h_bytes = 0
+        for m in self.models:
+            n = m.flat_size
+            b = dict(model=m, stream=torch.cuda.Stream(self.device),
+                     z_pin=torch.zeros(n, dtype=torch.float32).pin_memory(),
+                     grad_pin=torch.zeros(n, dtype=torch.float32).pin_memory(),
+                     out_pin=torch.zeros(8, dtype=torch.float64).pin_memory(),
+                     z_dev=torch.zeros(n, dtype=torch.float32, device=self.device),
+                     grad_dev=torch.zeros(n, dtype=torch.float32, device=self.device),
+                     out_dev=torch.zeros(8, dtype=torch.float64, device=self.device))
+            self.blocks.append(b)
+            self.h2d_bytes += n * 4
+            self.d2h_bytes += n * 4 + 6 * 8
+        self.z_views = [m.unflatten(b["z_pin"].numpy()) for m, b in zip(self.models, self.blocks)]
+        self.grad_views = [m.unflatten(b["grad_pin"].numpy()) for m, b in zip(self.models, self.blocks)]
+        self.launches = 0
+        self._sum = torch.zeros(6, dtype=torch.float64, device=self.device)
+
+    def set_hyper(self, values):
+        for b in self.blocks:
+            b["z_pin"][: self.n_hyper] = self.torch.as_tensor(np.asarray(values, np.float32))
+
+    def load_blocks(self, z_blocks):
+        """z_blocks[b]: flat float32 vector of block b in the block model's ``flatten`` order."""
+        for b, z in zip(self.blocks, z_blocks):
+            b["z_pin"].copy_(self.torch.as_tensor(np.asarray(z, np.float32)))
+
+    def value_and_grad_host(self):
+        """Returns (U, dU/dhyper[5], grad_views): per-star gradients are left in the pinned block buffers."""
+        torch = self.torch
+        for b in self.blocks:
+            with torch.cuda.stream(b["stream"]):
+                b["z_dev"].copy_(b["z_pin"], non_blocking=True)
+                b["model"].potential_device(b["z_dev"].data_ptr(), b["out_dev"].data_ptr(), b["grad_dev"].data_ptr(),
+                                            b["stream"].cuda_stream)
+                b["grad_pin"].copy_(b["grad_dev"], non_blocking=True)
+                b["out_pin"].copy_(b["out_dev"], non_blocking=True)
+            self.launches += 1
+        for b in self.blocks:
+            b["stream"].synchronize()
+        tot = np.sum([b["out_pin"][:6].numpy() for b in self.blocks], axis=0)
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            self._sum.copy_(torch.as_tensor(tot))
+            dist.all_reduce(self._sum, group=self.group)
+            tot = self._sum.cpu().numpy()
+        return float(tot[0]), tot[1:6].copy(), self.grad_views

@@ -155,3 +155,31 @@ def test_full_size_properties(n):
         assert np.array_equal(blocks[0], blocks[-1]) and np.array_equal(blocks[0], blocks[reps // 2])
         l2 = np.linalg.norm(blocks[0] - g_ref[k]) / np.linalg.norm(g_ref[k])
         assert l2 <= 2e-3, (k, l2)
+
+
+@pytest.mark.gpu
+def test_pipelined_host_blocks_reproduce_single_handle():
+    """parallel.PipelinedHostPotential (the end-to-end host-buffer API: blocks on streams) == one handle."""
+    import scalable_stellar_inference_b200 as ssi
+    from scalable_stellar_inference_b200.parallel import PipelinedHostPotential, shard_problem
+    name, n, nb = "hier_phot_grid", 1000, 3
+    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, n)
+    full = PU.product_model(name, n, "tcgen05").condition(obs, diag, M_H_loc=ml, M_H_scale=ms)
+    out, grad = full.potential_and_grad_flat(full.flatten(z0))
+    g_full = full.unflatten(grad)
+    blocks, zb = [], []
+    for b in range(nb):
+        m = PU.product_model(name, n, "tcgen05")
+        m.set_shard(b, nb)
+        zl, o, d, a, s = shard_problem(z0, obs, diag, ml, ms, b, nb)
+        m.condition(o, d, M_H_loc=a, M_H_scale=s)
+        blocks.append(m); zb.append(m.flatten(zl))
+    pipe = PipelinedHostPotential(blocks)
+    pipe.load_blocks(zb)
+    for _ in range(2):
+        u, gh, gviews = pipe.value_and_grad_host()
+    assert abs(u - out[0]) <= 1e-9 * abs(out[0])
+    assert np.allclose(gh, out[1:6], rtol=1e-9, atol=1e-9 * np.abs(out[1:6]).max())
+    for site in spec.star_sites():
+        cat = np.concatenate([gv[site] for gv in gviews])
+        assert np.array_equal(cat, g_full[site]), site

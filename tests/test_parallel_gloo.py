@@ -94,3 +94,13 @@ def test_two_rank_allreduce_reproduces_unsharded_potential():
     for k in spec.star_sites():
         full = np.concatenate([ret[r][1][k] for r in range(world)])
         np.testing.assert_allclose(full, g[k], rtol=1e-12, atol=1e-12)
+
+
+def test_block_bounds_are_round_aligned_and_cover_the_range():
+    from scalable_stellar_inference_b200.parallel import block_bounds
+    unit = 2 * 128 * 148
+    for lo, hi, nb in ((0, 1_000_000, 6), (500_000, 1_000_000, 4), (0, 700, 6), (3, 3 + unit, 5), (0, 10 * unit, 3)):
+        b = block_bounds(lo, hi, nb, unit)
+        assert b[0][0] == lo and b[-1][1] == hi and len(b) <= nb
+        assert all(x[1] == y[0] for x, y in zip(b, b[1:]))
+        assert all((e - s) % unit == 0 for s, e in b[:-1])          # only the last block may be partial
