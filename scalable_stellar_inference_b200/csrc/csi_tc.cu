@@ -260,9 +260,12 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long long n = io.n;
   const long long n_tiles = (n + kTile - 1) / kTile;
-  const long long n_pairs = (n_tiles + 1) / 2;
-  long long my_pairs = 0;
-  if ((long long)blockIdx.x < n_pairs) my_pairs = (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  // Work assignment at TILE granularity: tile k belongs to CTA k % grid; a CTA's tiles alternate between its two
+  // tile slots (slot 0 takes the 1st, 3rd, ... -- one more than slot 1 when the count is odd).  Each slot has its
+  // own epilogue warpgroup, MMA issuer and weight loader, so the slots simply run different iteration counts.
+  long long my_tiles = 0;
+  if ((long long)blockIdx.x < n_tiles) my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  auto slot_iters = [&](int slot) { return (my_tiles + 1 - slot) / 2; };
 
   // ---- one-time setup ----------------------------------------------------------------------------
   for (int i = tid; i < kSmallFloats; i += kThreads) S.small[i] = __ldg(L.tc.small + i);
@@ -318,7 +321,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     // with the next stage's half as soon as the MMAs that read it have completed (tcgen05.commit -> w_empty).
     const int t = warp - 10;
     if (lane == 0) {
-      const long long total = my_pairs * kNRing * 2;
+      const long long total = slot_iters(t) * kNRing * 2;
       for (long long it = 0; it < total; ++it) {
         const int hh = (int)(it & 1);
         const long long q = it >> 1;           // ring stage counter of this tile
@@ -366,7 +369,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     constexpr int kGateStage = PREDICT ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
     uint32_t k = 0, q = 0;            // stage counter of the tile's whole life (region parity); streamed-stage counter
     uint32_t apar0 = 0u, apar1 = 0u;  // parities of the next phases of a_ready[t][0 / 1]
-    for (long long p = 0; p < my_pairs; ++p) {
+    const long long my_iters = slot_iters(t);
+    for (long long p = 0; p < my_iters; ++p) {
 #pragma unroll 1
       for (int s = 0; s < kNStages; ++s, ++k) {
         const bool ring = ring_stage(s);
@@ -450,10 +454,11 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     long long it = 0;
     // Start gate: tile B begins a quarter of an evaluation chain after tile A, so that the long CUDA-core phases
     // of one tile (priors; table gather + likelihood; gradient stores) run under the MMA stages of the other.
-    if (t == 1 && my_pairs > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
-    for (long long p = 0; p < my_pairs; ++p) {
-      const long long pair = (long long)blockIdx.x + p * gridDim.x;
-      const long long i = (pair * 2 + t) * kTile + row;
+    const long long my_iters = slot_iters(t);
+    if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
+    for (long long p = 0; p < my_iters; ++p) {
+      const long long tile = (long long)blockIdx.x + (2 * p + t) * gridDim.x;
+      const long long i = tile * kTile + row;
       const bool valid = i < n;
       // pull the next pair's inputs of this warp's 32 stars towards L2 (two lanes cover the <= 2 lines per array)
       {
@@ -761,8 +766,7 @@ static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *sme
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return -(int)e;
   const long long n_tiles = (L.io.n + tc::kTile - 1) / tc::kTile;
-  const long long n_pairs = (n_tiles + 1) / 2;
-  const int grid = (int)std::min<long long>(n_pairs, L.sm_count);
+  const int grid = (int)std::min<long long>(n_tiles, L.sm_count);
   kern<<<grid, tc::kThreads, smem, st>>>(L);
   e = cudaGetLastError();
   if (e != cudaSuccess) return -(int)e;
