@@ -328,7 +328,11 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
     else if (cfg->bands > 0 && cfg->bc_mode == CSI_BC_NET)
       rc = fail(CSI_EINVAL, "tcgen05 engine: BC-emulator net inside the potential is not supported yet; use "
                             "CSI_ENGINE_FFMA or the BC table");
-    else {
+  }
+  // The tensor-core weight images are built whenever the emulator has the supported shape: the potential uses them
+  // with CSI_ENGINE_TCGEN05, the emulator operator (csi_net_forward / csi_net_vjp, which = 0) with either engine.
+  if (rc == CSI_OK && tc_supported(cfg->emulator)) {
+    {
       std::vector<uint8_t> img(tc_image_bytes(cfg->emulator)), resident(tc_resident_bytes(cfg->emulator));
       std::vector<float> small(tc_small_floats(cfg->emulator));
       tc_build_images(cfg->emulator, img.data(), resident.data(), small.data(), &h->tc.act_scale, &h->tc.w_scale);
@@ -535,11 +539,23 @@ static const NetDev *pick_net(csi_handle *h, int which) {
   return nullptr;
 }
 
+static const int64_t kNetTcMinRows = 2048;
+
 extern "C" int csi_net_forward(csi_handle *h, int32_t which, const float *x, float *y, int64_t n, void *stream) {
   if (!h || !x || !y || n < 0) return fail(CSI_EINVAL, "bad argument");
   const NetDev *net = pick_net(h, which);
   if (!net) return fail(CSI_EINVAL, "network not loaded");
-  int rc = launch_net_forward(*net, x, y, n, (cudaStream_t)stream);
+  int rc;
+  if (which == 0 && h->tc.img && n >= kNetTcMinRows) {
+    // large batches of the stellar emulator: the tcgen05 kernel in operator mode (small ones keep the CUDA-core
+    // kernel and its plain fp32 k-order accumulation, which the single-point known-answer tests pin to 5e-7)
+    Launch L;
+    memset(&L, 0, sizeof(L));
+    L.tc = h->tc; L.io.n = n; L.net_x = x; L.net_y = y; L.sm_count = h->sm_count;
+    rc = launch_net_tc(L, false, (cudaStream_t)stream);
+  } else {
+    rc = launch_net_forward(*net, x, y, n, (cudaStream_t)stream);
+  }
   if (rc < 0) return fail(CSI_ECUDA, std::string("net_forward: ") + cudaGetErrorString((cudaError_t)(-rc)));
   return CSI_OK;
 }
@@ -549,7 +565,15 @@ extern "C" int csi_net_vjp(csi_handle *h, int32_t which, const float *x, const f
   if (!h || !x || !gy || !gx || n < 0) return fail(CSI_EINVAL, "bad argument");
   const NetDev *net = pick_net(h, which);
   if (!net) return fail(CSI_EINVAL, "network not loaded");
-  int rc = launch_net_vjp(*net, x, gy, gx, n, (cudaStream_t)stream);
+  int rc;
+  if (which == 0 && h->tc.img && n >= kNetTcMinRows) {
+    Launch L;
+    memset(&L, 0, sizeof(L));
+    L.tc = h->tc; L.io.n = n; L.net_x = x; L.net_gy = gy; L.net_gx = gx; L.sm_count = h->sm_count;
+    rc = launch_net_tc(L, true, (cudaStream_t)stream);
+  } else {
+    rc = launch_net_vjp(*net, x, gy, gx, n, (cudaStream_t)stream);
+  }
   if (rc < 0) return fail(CSI_ECUDA, std::string("net_vjp: ") + cudaGetErrorString((cudaError_t)(-rc)));
   return CSI_OK;
 }

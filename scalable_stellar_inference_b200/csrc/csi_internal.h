@@ -34,6 +34,8 @@ struct Launch {           // everything a potential launch needs
   float *grad_hyper;      // may be null
   float *mean_out;        // predict mode only: [n][kMaxMean]
   float *params_out;      // predict mode only: [n][8]
+  const float *net_x, *net_gy;  // emulator-operator modes: x [n][5], gy [n][4]
+  float *net_y, *net_gx;        // y [n][4], gx [n][5]
   int sm_count;
 };
 
@@ -42,6 +44,7 @@ int launch_potential_ffma(const Launch &L, cudaStream_t st, int *grid_out, int *
 int launch_potential_tc(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out);
 int launch_predict_ffma(const Launch &L, cudaStream_t st);
 int launch_predict_tc(const Launch &L, cudaStream_t st);
+int launch_net_tc(const Launch &L, bool vjp, cudaStream_t st);
 int launch_net_forward(const NetDev &net, const float *x, float *y, long long n, cudaStream_t st);
 int launch_net_vjp(const NetDev &net, const float *x, const float *gy, float *gx, long long n, cudaStream_t st);
 int launch_grid_forward(const GridDev &g, int bands, const float *x, float *y, long long n, cudaStream_t st);

@@ -247,11 +247,16 @@ struct Tracer {
 
 __device__ __forceinline__ bool ring_stage(int s) { return (s >= 1 && s <= 5) || (s >= 8 && s <= 12); }
 
-// PREDICT = forward only (stages 0..6): writes predict's means / parameters instead of gradients (csi_predict).
-template <int BC, bool PREDICT>
+// MODE 0: the potential.  MODE 1 (predict): forward only (stages 0..6), writes predict's means / parameters instead
+// of gradients (csi_predict).  MODE 2 / 3: the emulator operator on its own (csi_net_forward / csi_net_vjp, plug
+// point Emulator(backend)): x[n,5] -> y[n,4], and (x, gy) -> gx[n,5]; no priors, likelihood or reduction.
+enum Mode { M_POTENTIAL = 0, M_PREDICT = 1, M_NET_FWD = 2, M_NET_VJP = 3 };
+template <int BC, int MODE>
 __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_constant__ Launch L) {
-  constexpr int kNStages = PREDICT ? 7 : kStages;
-  constexpr int kNRing = PREDICT ? 5 : kRingImages;
+  constexpr bool PREDICT = MODE == M_PREDICT, NET = MODE == M_NET_FWD || MODE == M_NET_VJP;
+  constexpr bool FWD_ONLY = MODE == M_PREDICT || MODE == M_NET_FWD;
+  constexpr int kNStages = FWD_ONLY ? 7 : kStages;
+  constexpr int kNRing = FWD_ONLY ? 5 : kRingImages;
   extern __shared__ unsigned char smem_raw[];
   // align inside the shared window (keeps the pointer provably in the shared address space: LDS/STS, not LD/ST)
   Smem &S = *reinterpret_cast<Smem *>(smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u));
@@ -366,7 +371,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       }
     };
     Tracer tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
-    constexpr int kGateStage = PREDICT ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
+    constexpr int kGateStage = FWD_ONLY ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
     uint32_t k = 0, q = 0;            // stage counter of the tile's whole life (region parity); streamed-stage counter
     uint32_t apar0 = 0u, apar1 = 0u;  // parities of the next phases of a_ready[t][0 / 1]
     const long long my_iters = slot_iters(t);
@@ -483,6 +488,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         st.x[0] = 0.3f; st.x[1] = 1.1f; st.x[2] = 0.1f; st.x[3] = 0.27f; st.x[4] = 2.0f; st.tau = 1.0f; st.dist = 100.f;
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
+      } else if (valid && NET) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) x[k] = (L.net_x[i * 5 + k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else if (valid) {
         star_pre(m, hv, io, i, st, acc);
 #pragma unroll
@@ -537,11 +545,20 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             for (int c = 0; c < 4; ++c) o[c] = sm[oOutLoc + c] + sm[oOutScale + c] * (__uint_as_float(r8[c]) * inv_fwd);
             float mean_local[kMaxMean];
             float *mo = PREDICT ? mean_local : nullptr;
+            if (NET) {
+              if (MODE == M_NET_FWD) {
+                *reinterpret_cast<float4 *>(L.net_y + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
+              } else {
+                const float4 gq = *reinterpret_cast<const float4 *>(L.net_gy + i * 4);
+                g_o[0] = gq.x; g_o[1] = gq.y; g_o[2] = gq.z; g_o[3] = gq.w;
+              }
+            } else {
             StarObs so;
             star_load_obs(m, io, i, so);
             if (L.tc.debug & 2) { g_o[0] = o[0]; g_o[1] = o[1]; g_o[2] = o[2]; g_o[3] = o[3]; }
             else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
             else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
+            }
 #pragma unroll
             for (int c = 0; c < 4; ++c) g_y[c] = g_o[c] * sm[oOutScale + c];
             if (PREDICT) {
@@ -556,7 +573,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
               }
             }
           }
-          if (!PREDICT) {
+          if (!FWD_ONLY) {
             // [g_hi(4) | g_lo(4) | g_hi(4) | 0(4)] with a per-row power-of-two scale, K = 16 -> 8 columns
             const float gmax = fmaxf(fmaxf(fabsf(g_y[0]), fabsf(g_y[1])), fmaxf(fabsf(g_y[2]), fabsf(g_y[3])));
             const float f = pow2_scale(gmax);
@@ -594,12 +611,17 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             float g_x[5];
 #pragma unroll
             for (int k = 0; k < 5; ++k) g_x[k] = __uint_as_float(r8[k]) * un * sm[oInInv + k];
-            star_post(m, io, i, st, g_x);
-            acc.lp += (double)st.lp;
+            if (NET) {
+#pragma unroll
+              for (int k = 0; k < 5; ++k) L.net_gx[i * 5 + k] = g_x[k];
+            } else {
+              star_post(m, io, i, st, g_x);
+              acc.lp += (double)st.lp;
+            }
           }
         }
         tr.rec(300 + s);
-        if (s == 6 && !PREDICT) {
+        if (s == 6 && !FWD_ONLY) {
           publish_a(0);  // the narrow A operand of stage 7 (the 128-wide stages publish chunk by chunk above)
           tr.rec(400 + s);
         } else if (s == kNStages - 1) {
@@ -614,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);
-  if (!PREDICT) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
+  if (MODE == M_POTENTIAL) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
 }
 
 }  // namespace tc
@@ -759,10 +781,10 @@ void tc_build_images(const csi_net &net, uint8_t *img, uint8_t *res, float *smal
   }
 }
 
-template <int BC, bool PREDICT>
+template <int BC, int MODE>
 static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out) {
   const int smem = (int)sizeof(tc::Smem) + 1024;
-  auto kern = tc::potential_tc_kernel<BC, PREDICT>;
+  auto kern = tc::potential_tc_kernel<BC, MODE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return -(int)e;
   const long long n_tiles = (L.io.n + tc::kTile - 1) / tc::kTile;
@@ -776,13 +798,18 @@ static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *sme
 }
 
 int launch_potential_tc(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out) {
-  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, false>(L, st, grid_out, smem_out);
-  return launch_tc_t<0, false>(L, st, grid_out, smem_out);
+  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, tc::M_POTENTIAL>(L, st, grid_out, smem_out);
+  return launch_tc_t<0, tc::M_POTENTIAL>(L, st, grid_out, smem_out);
 }
 
 int launch_predict_tc(const Launch &L, cudaStream_t st) {
-  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, true>(L, st, nullptr, nullptr);
-  return launch_tc_t<0, true>(L, st, nullptr, nullptr);
+  if (L.model.bands > 0 && L.model.bc_mode == 1) return launch_tc_t<1, tc::M_PREDICT>(L, st, nullptr, nullptr);
+  return launch_tc_t<0, tc::M_PREDICT>(L, st, nullptr, nullptr);
+}
+
+// the stellar emulator on its own on the tensor-core engine: L.io.n rows, L.net_* pointers set
+int launch_net_tc(const Launch &L, bool vjp, cudaStream_t st) {
+  return vjp ? launch_tc_t<0, tc::M_NET_VJP>(L, st, nullptr, nullptr) : launch_tc_t<0, tc::M_NET_FWD>(L, st, nullptr, nullptr);
 }
 
 }  // namespace csi
