@@ -155,7 +155,7 @@ def run_reference(args):
         "note": "reference JAX-CPU unavailable on this box (jax, numpyro, h5py not installed, no network): the CPU "
                 "restatement of the same path is timed instead",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, engine):
@@ -308,12 +308,25 @@ def run_b200(args):
         if world == 1 and not args.no_cpu_baseline:
             rate, cores, desc, _ = cpu_reference_rate(args.stars, args.cpu_sample, budget_s=15.0)
             line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line: dict):
+    """The ONE JSON line on the real stdout (library banners such as NCCL's version line go to stderr)."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
+_REAL_STDOUT = None
+
 if __name__ == "__main__":
+    # keep stdout clean for the single JSON line: everything else that writes to fd 1 (NCCL prints
+    # "NCCL version ..." there) is redirected to stderr for the whole run
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)
