@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=20_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
+    ap.add_argument("--nccl-allreduce", action="store_true", help="keep the NCCL allreduce instead of the in-kernel exchange")
     ap.add_argument("--e2e-blocks", type=int, default=6, help="star blocks of the pipelined host-buffer path")
     return ap.parse_args()
 
@@ -162,7 +163,9 @@ def workload_config(args, engine):
     return {"workload": "BASELINE config 4: HierarchicalStarModel spec+phot, observables "
                         "[log_Teff, log_g, mag(G,BP,RP), plx], kind=diag, BC table 70x26x18x13 (synthetic MIST stand-in)",
             "stars": args.stars, "sites_per_star": 7, "hyper_sites": 5, "engine": engine,
-            "parallelism": f"star-sharded x{args.gpus}, one 6-double allreduce per evaluation",
+            "parallelism": f"star-sharded x{args.gpus}, one 6-double allreduce per evaluation"
+                           + (" (fused into the kernel over NVLink peer memory)" if getattr(args, "fused", False) else
+                              (" (NCCL)" if args.gpus > 1 else "")),
             "l2": "no-flush" if args.no_flush else "L2 flushed (256 MiB write) between timed evaluations"}
 
 
@@ -195,6 +198,16 @@ def run_b200(args):
     zl, obs_l, diag_l, ml_l, ms_l = shard_problem(z0, obs, diag, ml, ms, rank, world)
     model.condition(obs_l, diag_l, M_H_loc=ml_l, M_H_scale=ms_l)
     pot = ShardedPotential(model)
+    u_nccl = None
+    if world > 1 and not args.nccl_allreduce:
+        # reference value through NCCL first, then switch the handle to the in-kernel exchange over peer memory
+        pot.z_pin.copy_(torch.from_numpy(model.flatten(zl))); pot.z_dev.copy_(pot.z_pin)
+        pot.value_and_grad_device(); torch.cuda.synchronize(dev)
+        u_nccl = pot.out_dev[:6].clone()
+        from scalable_stellar_inference_b200.parallel import setup_peer_exchange
+        pot.exchange = setup_peer_exchange(model)
+    fused = pot.exchange is not None
+    args.fused = fused
     pot.z_pin.copy_(torch.from_numpy(model.flatten(zl)))
     pot.z_dev.copy_(pot.z_pin)
     flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -208,6 +221,9 @@ def run_b200(args):
         pot.value_and_grad_device()
     torch.cuda.synchronize(dev)
     u_first = float(pot.out_dev[0].item())
+    if fused and u_nccl is not None:
+        if not torch.allclose(pot.out_dev[:6], u_nccl, rtol=1e-12, atol=0.0):
+            raise SystemExit(f"fused exchange {pot.out_dev[:6].tolist()} differs from NCCL {u_nccl.tolist()}")
     if not np.isfinite(u_first) and not os.environ.get("CSI_TC_DEBUG"):
         raise SystemExit(f"non-finite potential {u_first}")
 
@@ -227,7 +243,7 @@ def run_b200(args):
         model.potential_device(pot.z_dev.data_ptr(), pot.out_dev.data_ptr(), pot.grad_dev.data_ptr(), stream)
         pot.launches += 1
         ev[k][1].record()
-        if world > 1:
+        if world > 1 and not fused:
             dist.all_reduce(pot.out_dev[:6])
         ev[k][2].record()
     barrier()

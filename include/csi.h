@@ -117,6 +117,15 @@ void csi_destroy(csi_handle *h);
  * (replicated) hyper-prior terms are added on rank 0 only so that a SUM-allreduce of `out` is exact. */
 int csi_set_shard(csi_handle *h, int32_t rank, int32_t world);
 
+/* Fused allreduce of `out` (no reference equivalent: the reference never shards the star axis).  peer_bufs[r] is
+ * a device pointer, valid in THIS process, to rank r's exchange buffer of 2 * world * 8 doubles, zero-initialised
+ * and writable by all ranks over NVLink peer memory (CUDA IPC / symmetric memory; peer_bufs[rank] is the caller's
+ * own).  Afterwards the finalising block of every csi_potential stores its 6 sums into all ranks' buffers and adds
+ * the world's contributions in rank order, so `out` (and the hyper slots of grad) hold the GLOBAL sums and no
+ * separate collective call is needed.  All ranks must call csi_potential the same number of times.  world <= 1
+ * or peer_bufs == NULL switches it off. */
+int csi_set_peer_exchange(csi_handle *h, int32_t world, int32_t rank, void *const *peer_bufs);
+
 /* Observations of the local stars.  Replaces the `obs=` / `diag=` arguments of model.__call__
  * (numpyro_models.py:242,255,341) and the per-star M_H prior arrays of scripts/model_star.py:126-128.
  * obs, diag: host, row-major [n_local, n_obs] (diag may be NULL = 0).  mh_loc / mh_scale: host [n_local]

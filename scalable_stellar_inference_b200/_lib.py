@@ -65,6 +65,7 @@ _PROTOS = {
     "csi_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
     "csi_destroy": (None, [C.c_void_p]),
     "csi_set_shard": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
+    "csi_set_peer_exchange": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "csi_set_data": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "csi_layout": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p)]),
     "csi_potential": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -393,6 +393,20 @@ extern "C" int csi_set_shard(csi_handle *h, int32_t rank, int32_t world) {
   return CSI_OK;
 }
 
+extern "C" int csi_set_peer_exchange(csi_handle *h, int32_t world, int32_t rank, void *const *peer_bufs) {
+  if (!h) return fail(CSI_EINVAL, "null handle");
+  if (world <= 1 || !peer_bufs) { h->px = csi::PeerX{}; return CSI_OK; }  // off: out6 holds the local sums
+  if (world > csi::kMaxPeers || rank < 0 || rank >= world) return fail(CSI_EINVAL, "peer exchange: world <= 8, 0 <= rank < world");
+  csi::PeerX px{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_bufs[r]) return fail(CSI_EINVAL, "peer exchange: null buffer");
+    px.bufs[r] = static_cast<double *>(peer_bufs[r]);
+  }
+  px.world = world; px.rank = rank; px.epoch = 0;
+  h->px = px;
+  return CSI_OK;
+}
+
 extern "C" int csi_layout(const csi_handle *h, int32_t *n_hyper, int32_t *n_star_sites, const char **names) {
   if (!h) return fail(CSI_EINVAL, "null handle");
   if (n_hyper) *n_hyper = h->n_hyper;
@@ -488,6 +502,7 @@ static void fill_launch(const csi_handle *h, const float *z, double *out6, float
   L.counter = h->d_counter;
   L.out6 = out6;
   L.grad_hyper = (grad && h->n_hyper) ? grad : nullptr;
+  L.px = h->px;
   L.sm_count = h->sm_count;
 }
 
@@ -495,6 +510,7 @@ extern "C" int csi_potential(csi_handle *h, const float *z_dev, double *out_dev,
   if (!h || !z_dev || !out_dev || !grad_dev) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
   Launch L;
+  if (h->px.world > 1) ++h->px.epoch;  // one collective epoch per evaluation, the same count on every rank
   fill_launch(h, z_dev, out_dev, grad_dev, L);
   cudaStream_t st = (cudaStream_t)stream;
   int rc = h->engine == CSI_ENGINE_TCGEN05 ? launch_potential_tc(L, st, &h->last_grid, &h->last_smem)

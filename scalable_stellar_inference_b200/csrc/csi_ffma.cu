@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kRows) potential_ffma_kernel(const __grid_cons
       acc.lp += (double)st.lp;
     }
   }
-  if (!PREDICT) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
+  if (!PREDICT) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper, L.px);
 }
 
 template <int BC, bool PREDICT>

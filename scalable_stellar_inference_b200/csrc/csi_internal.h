@@ -8,6 +8,7 @@
 
 #include "../../include/csi.h"
 #include "csi_net.cuh"
+#include "csi_reduce.cuh"
 
 namespace csi {
 
@@ -36,6 +37,7 @@ struct Launch {           // everything a potential launch needs
   float *params_out;      // predict mode only: [n][8]
   const float *net_x, *net_gy;  // emulator-operator modes: x [n][5], gy [n][4]
   float *net_y, *net_gx;        // y [n][4], gx [n][5]
+  PeerX px;               // fused allreduce over peer memory (world <= 1: off)
   int sm_count;
 };
 
@@ -86,6 +88,7 @@ struct csi_handle {
   double *h_out = nullptr, *d_out = nullptr;
   long long stage_len = 0;
   cudaStream_t stream = nullptr;
+  csi::PeerX px{};          // csi_set_peer_exchange
   long long last_launches = 0;
   int last_grid = 0, last_smem = 0;
 };

@@ -636,7 +636,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::tc_fence_before();
   __syncthreads();
   if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);
-  if (MODE == M_POTENTIAL) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper);
+  if (MODE == M_POTENTIAL) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper, L.px);
 }
 
 }  // namespace tc

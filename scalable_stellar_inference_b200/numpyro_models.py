@@ -202,6 +202,16 @@ class SingleStarModel:
         self._rank, self._world = rank, world
         return self
 
+    def set_peer_exchange(self, peer_ptrs):
+        """Fuse the allreduce of the 6 sums into the kernel: ``peer_ptrs[r]`` = device pointer (valid in this
+        process) to rank r's exchange buffer (csi_set_peer_exchange); ``None`` switches it off."""
+        if not peer_ptrs:
+            _lib.check(self._lib.csi_set_peer_exchange(self._h, 1, 0, None))
+            return self
+        arr = (C.c_void_p * len(peer_ptrs))(*[C.c_void_p(int(p)) for p in peer_ptrs])
+        _lib.check(self._lib.csi_set_peer_exchange(self._h, len(peer_ptrs), self._rank, arr))
+        return self
+
     def condition(self, obs, diag=None, M_H_loc=None, M_H_scale=None):
         """Load the observations of the LOCAL stars: ``obs`` / ``diag`` are [n, k] with k observed columns
         (``"mag"`` expands to one column per band); ``diag=None`` is 0 as in ``likelihood`` (``:229-230``)."""

@@ -64,6 +64,38 @@ def allreduce_out(out, group=None):
     return out
 
 
+def setup_peer_exchange(model, group=None):
+    """Map every rank's exchange buffer into this process (PyTorch symmetric memory over NVLink peer access) and
+    hand the pointers to libcsi: the 6-double allreduce is then done by the finalising block of the potential
+    kernel itself (csi_set_peer_exchange) -- no NCCL call per evaluation.  Returns an object that must be kept
+    alive, or None when symmetric memory is unavailable (the caller keeps the NCCL allreduce)."""
+    import sys
+    import torch
+    import torch.distributed as dist
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        if world < 2 or world > 8:
+            return None
+        dev = torch.device("cuda", model.device)
+        n = 2 * world * 8
+        buf = symm_mem.empty(n, dtype=torch.float64, device=dev)
+        buf.zero_()
+        hdl = symm_mem.rendezvous(buf, group if group is not None else dist.group.WORLD)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        torch.cuda.synchronize(dev)
+        dist.barrier(group)                      # every buffer is zeroed before anybody's kernel writes into it
+        model.set_peer_exchange(ptrs)
+        return dict(buf=buf, handle=hdl, ptrs=ptrs, world=world, rank=rank)
+    except Exception as e:  # noqa: BLE001 -- any failure here just means "use NCCL"
+        print(f"[parallel] fused peer exchange unavailable ({type(e).__name__}: {e}); using NCCL", file=sys.stderr)
+        try:
+            model.set_peer_exchange(None)
+        except Exception:  # noqa: BLE001
+            pass
+        return None
+
+
 class ShardedPotential:
     """The repo's public evaluation object for 1..8 GPUs.
 
@@ -72,11 +104,13 @@ class ShardedPotential:
     ``value_and_grad_host`` is the end-to-end call: pinned host z -> device, evaluate, allreduce, device -> host.
     """
 
-    def __init__(self, model, group=None):
+    def __init__(self, model, group=None, fused=False):
         import torch
         self.torch = torch
         self.model, self.group = model, group
         self.device = torch.device("cuda", model.device)
+        # fused=True: the kernel itself exchanges the 6 sums over peer memory (setup_peer_exchange)
+        self.exchange = setup_peer_exchange(model, group) if fused else None
         n = model.flat_size
         self.n_hyper = len(model.hyper_sites)
         self.z_dev = torch.zeros(n, dtype=torch.float32, device=self.device)
@@ -95,7 +129,8 @@ class ShardedPotential:
         stream = torch.cuda.current_stream(self.device).cuda_stream
         self.model.potential_device(z.data_ptr(), self.out_dev.data_ptr(), self.grad_dev.data_ptr(), stream)
         self.launches += 1
-        allreduce_out(self.out_dev[:6], self.group)
+        if self.exchange is None:
+            allreduce_out(self.out_dev[:6], self.group)
         return self.out_dev, self.grad_dev
 
     def value_and_grad_host(self, z_host=None):
