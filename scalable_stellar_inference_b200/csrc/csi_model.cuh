@@ -283,6 +283,19 @@ CSI_DEV void star_load_z(const DevModel &m, const StarIO &io, long long i, StarI
   in.mlogz = io.mh_logz ? io.mh_logz[i] : m.mh.lognorm;
 }
 
+// The tcgen05 kernel stages a star's inputs through a per-thread column of shared memory with asynchronous copies
+// issued most of a tile ahead (csi_tc.cu): rows 0..8 the sites and 9..11 the [Fe/H] prior while the priors are
+// pending, then rows k / kMaxMean + k the observation / extra variance of mean k until star_mid has read them.
+constexpr int kStageRows = 2 * kMaxMean;
+constexpr int kStageStride = 256;  // one column per epilogue thread
+CSI_DEV void star_take_z(const DevModel &m, const StarIO &io, const float *col, StarIn &in) {
+#pragma unroll
+  for (int s = 0; s < kSlots; ++s) in.zv[s] = io.z[s] ? col[s * kStageStride] : 0.0f;
+  in.mloc = io.mh_loc ? col[9 * kStageStride] : m.mh.loc;
+  in.mscale = io.mh_scale ? col[10 * kStageStride] : m.mh.inv_scale;
+  in.mlogz = io.mh_logz ? col[11 * kStageStride] : m.mh.lognorm;
+}
+
 CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, StarState &st, HyperAcc &acc) {
   float lp = 0.0f;
   const float *zv = in.zv;
@@ -565,6 +578,15 @@ CSI_DEV void star_load_obs(const DevModel &m, const StarIO &io, long long i, Sta
     const bool on = m.kind == 0 && io.obsm[k] != nullptr;
     so.ob[k] = on ? io.obsm[k][i] : 0.0f;
     so.dg[k] = (on && io.diagm[k]) ? io.diagm[k][i] : 0.0f;
+  }
+}
+
+CSI_DEV void star_take_obs(const DevModel &m, const StarIO &io, const float *col, StarObs &so) {
+#pragma unroll
+  for (int k = 0; k < kMaxMean; ++k) {
+    const bool on = m.kind == 0 && io.obsm[k] != nullptr;
+    so.ob[k] = on ? col[k * kStageStride] : 0.0f;
+    so.dg[k] = (on && io.diagm[k]) ? col[(kMaxMean + k) * kStageStride] : 0.0f;
   }
 }
 

@@ -62,6 +62,12 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
 
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// 4-byte asynchronous global -> shared copy (LDGSTS): no register holds the value in flight; the issuing thread sees
+// the data after cp_async_wait_all()
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---- tcgen05: tensor memory -----------------------------------------------------------------------

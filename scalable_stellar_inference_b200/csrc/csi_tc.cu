@@ -88,6 +88,7 @@ struct __align__(128) Smem {
   uint8_t a_const[kBiasBytes];   // constant A tile of the bias MMA: columns k = 0..2 hold oBiasA, rest 0
   float small[kSmallFloats];
   uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
+  float stage[kStageRows][kStageStride];  // per-thread input staging column (star_take_z / star_take_obs)
   float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
   unsigned short grid_lut[4][kLutBins];
   uint64_t w_full[2][2], w_empty[2][2], a_ready[2][2], d_ready[2], start_b;  // a_ready: one barrier per K-half
@@ -95,6 +96,8 @@ struct __align__(128) Smem {
   double red[(kThreads / 32) * 6];
   HyperVals hv;
 };
+
+static_assert(sizeof(Smem) + 1024 <= 232448, "shared memory of one CTA");
 
 // byte offset of element (n, k) inside an operand image with 128 rows (no-swizzle K-major core matrices)
 __host__ __device__ constexpr uint32_t img_offset(int n, int k) {
@@ -460,27 +463,36 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     // Start gate: tile B begins a quarter of an evaluation chain after tile A, so that the long CUDA-core phases
     // of one tile (priors; table gather + likelihood; gradient stores) run under the MMA stages of the other.
     const long long my_iters = slot_iters(t);
+    // Input staging: a thread copies its star's inputs into its own column of S.stage with 4-byte asynchronous
+    // copies, most of a tile before it needs them -- the sites of tile p + 1 once star_mid of tile p has taken the
+    // observations out of the column, the observations of tile p once its priors have taken the sites.  Nothing
+    // but the thread itself touches the column, so cp.async.wait_all is the only synchronisation.
+    float *col = &S.stage[0][tid];
+    auto stage_sites = [&](long long ii) {
+      if (NET || ii >= n) return;
+#pragma unroll
+      for (int sl = 0; sl < kSlots; ++sl)
+        if (io.z[sl]) ptx::cp_async4(col + sl * kStageStride, io.z[sl] + ii);
+      if (io.mh_loc) ptx::cp_async4(col + 9 * kStageStride, io.mh_loc + ii);
+      if (io.mh_scale) ptx::cp_async4(col + 10 * kStageStride, io.mh_scale + ii);
+      if (io.mh_logz) ptx::cp_async4(col + 11 * kStageStride, io.mh_logz + ii);
+    };
+    auto stage_obs = [&](long long ii) {
+      if (NET || ii >= n || m.kind != 0) return;
+#pragma unroll
+      for (int k = 0; k < kMaxMean; ++k)
+        if (io.obsm[k]) {
+          ptx::cp_async4(col + k * kStageStride, io.obsm[k] + ii);
+          if (io.diagm[k]) ptx::cp_async4(col + (kMaxMean + k) * kStageStride, io.diagm[k] + ii);
+        }
+    };
+    if (my_iters > 0) stage_sites(((long long)blockIdx.x + t * gridDim.x) * kTile + row);
     if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
     for (long long p = 0; p < my_iters; ++p) {
       const long long tile = (long long)blockIdx.x + (2 * p + t) * gridDim.x;
       const long long i = tile * kTile + row;
       const bool valid = i < n;
-      // pull the next pair's inputs of this warp's 32 stars towards L2 (two lanes cover the <= 2 lines per array)
-      {
-        const long long inext = i + 2LL * kTile * gridDim.x;
-        if ((lane == 0 || lane == 31) && inext < n) {
-#pragma unroll
-          for (int sl = 0; sl < kSlots; ++sl)
-            if (io.z[sl]) ptx::prefetch_l2(io.z[sl] + inext);
-          for (int j = 0; j < m.n_obs; ++j) {
-            ptx::prefetch_l2(io.obs[j] + inext);
-            if (io.diag[j]) ptx::prefetch_l2(io.diag[j] + inext);
-          }
-          if (io.mh_loc) {
-            ptx::prefetch_l2(io.mh_loc + inext); ptx::prefetch_l2(io.mh_scale + inext); ptx::prefetch_l2(io.mh_logz + inext);
-          }
-        }
-      }
+      const long long i_next = p + 1 < my_iters ? i + 2LL * kTile * gridDim.x : n;  // same row, this slot's next tile
       StarState st;
       float x[5];
       if (valid && (L.tc.debug & 2)) {
@@ -492,9 +504,21 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = (L.net_x[i * 5 + k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else if (valid) {
-        star_pre(m, hv, io, i, st, acc);
+        tr.rec(501);
+        StarIn in;
+        ptx::cp_async_wait_all();
+        star_take_z(m, io, col, in);
+        if (tr.p) {  // trace only: stall until the loads have landed so that their latency shows up on its own
+          uint32_t x_ = __float_as_uint(in.mloc) ^ __float_as_uint(in.mscale) ^ __float_as_uint(in.mlogz);
+#pragma unroll
+          for (int sl = 0; sl < kSlots; ++sl) x_ ^= __float_as_uint(in.zv[sl]);
+          if (x_ == 0xdeadbeefu) tr.rec(999);
+          tr.rec(502);
+        }
+        star_pre(m, hv, in, st, acc);
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
+        if (tr.p) { if (x[0] + x[1] + x[2] + x[3] + x[4] + st.lp == 1.2345e30f) tr.rec(999); tr.rec(503); }
       } else {
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = 0.0f;
@@ -514,6 +538,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         ptx::tmem_st16(t_base + (uint32_t)(((it & 1) ^ 1) * 128), a0);  // A of stage `it` lives in the other region
       }
       publish_a(0);
+      if (!(L.tc.debug & 2)) stage_obs(i);  // the column is free: the priors hold the sites in registers
 
       float un = 1.0f;    // cotangent un-scaling: true value = D * un
       float amax = 0.0f;  // max |A operand| of the current VJP stage (after scaling)
@@ -554,10 +579,20 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
               }
             } else {
             StarObs so;
-            star_load_obs(m, io, i, so);
+            tr.rec(601);
+            ptx::cp_async_wait_all();
+            star_take_obs(m, io, col, so);
+            if (tr.p) {
+              uint32_t x_ = 0;
+#pragma unroll
+              for (int k = 0; k < kMaxMean; ++k) x_ ^= __float_as_uint(so.ob[k]) ^ __float_as_uint(so.dg[k]);
+              if (x_ == 0xdeadbeefu) tr.rec(999);
+              tr.rec(602);
+            }
             if (L.tc.debug & 2) { g_o[0] = o[0]; g_o[1] = o[1]; g_o[2] = o[2]; g_o[3] = o[3]; }
             else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
             else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
+            stage_sites(i_next);  // the observations have been consumed: the column takes the next tile's sites
             }
 #pragma unroll
             for (int c = 0; c < 4; ++c) g_y[c] = g_o[c] * sm[oOutScale + c];
