@@ -93,7 +93,12 @@ struct GridDev {
 // ---------------------------------------------------------------------------------------------
 // scalar helpers
 // ---------------------------------------------------------------------------------------------
-CSI_DEV float sigmoidf_(float u) { return 1.0f / (1.0f + expf(-u)); }
+// Fast forms for operands that are normal numbers of moderate size (MUFU-based, 1-2 ulp, no slow-path branch: an
+// IEEE divide or a libm call splits the basic block and serialises the otherwise independent per-site chains).
+CSI_DEV float rcp_(float x) { return __fdividef(1.0f, x); }
+CSI_DEV float exp_(float x) { return exp2f(x * 1.4426950408889634f); }
+CSI_DEV float log_(float x) { return __logf(x); }
+CSI_DEV float sigmoidf_(float u) { return rcp_(1.0f + exp_(-u)); }
 
 // log(s(1-s)) = -softplus(u) - softplus(-u) = -|u| - 2 log1p(exp(-|u|))
 CSI_DEV float log_sigmoid_prod(float u) {
@@ -105,10 +110,11 @@ CSI_DEV float log_sigmoid_prod(float u) {
 //   log(s (1 - s)) = -|u| - 2 l1,   log s = min(u, 0) - l1,   log(1 - s) = -max(u, 0) - l1
 CSI_DEV void sig_pair(float u, float &s, float &l1) {
   const float a = fabsf(u);
-  const float e = expf(-a);
-  const float inv = 1.0f / (1.0f + e);
+  const float e = exp_(-a);
+  const float w = 1.0f + e;
+  const float inv = rcp_(w);
   s = (u >= 0.0f) ? inv : e * inv;
-  l1 = log1pf(e);
+  l1 = log_(w);  // e in (0, 1]: absolute error ~2e-7 on a term added to O(1) log-densities
 }
 
 // log Phi(x), x <= 0 branch uses the scaled complementary error function (no underflow)
@@ -150,10 +156,10 @@ CSI_DEV void bounded_transform(const TnC &c, float u, float &v, float &dv, float
     ld = c.logw - fabsf(u) - 2.0f * l1;
     dld = 1.0f - 2.0f * s;
   } else if (c.kind == TN_UPPER) {
-    float e = expf(u);
+    float e = exp_(u);
     v = c.high - e; dv = -e; ld = u; dld = 1.0f;
   } else if (c.kind == TN_LOWER) {
-    float e = expf(u);
+    float e = exp_(u);
     v = c.low + e; dv = e; ld = u; dld = 1.0f;
   } else {
     v = u; dv = 1.0f; ld = 0.0f; dld = 0.0f;
@@ -204,7 +210,7 @@ CSI_DEV void tn_logpdf_grads(float x, float mu, float sigma, float low, float hi
 
 // Gamma(conc, rate) site with exp transform: log-term (log_prob + u) and d/du
 CSI_DEV void gamma_site(float u, float conc, float rate, float cst, float &x, float &lt, float &dlt) {
-  x = expf(u);
+  x = exp_(u);
   lt = cst + (conc - 1.0f) * u - rate * x + u;  // log x = u
   dlt = (conc - 1.0f) - rate * x + 1.0f;
 }
@@ -322,14 +328,14 @@ CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, S
   st.x[2] = mh; st.dmh = dv;
 
   float t = exp2f(-(mh + m.log_zx_sun) * kLog2_10);
-  float q = 1.0f / (1.0f + t);
+  float q = rcp_(1.0f + t);
   float dq_dmh = kLn10 * q * (1.0f - q);
   float g_mh_prior = 0.0f;
 
   if (m.prior_mode == P_HIER) {
     // decentred Y and a_MLT with star-/hyper-dependent bounds (:318-333); Y = ylo + w*sigmoid(u)
     float f = h.dydz * q;
-    float inv1f = 1.0f / (1.0f + f);
+    float inv1f = rcp_(1.0f + f);
     float mu_y = (h.y0 + f) * inv1f;
     float dmu_dy0 = inv1f;
     float dmu_df = (1.0f - h.y0) * inv1f * inv1f;
@@ -451,7 +457,7 @@ CSI_DEV int grid_locate(const float *g, const unsigned short *lut, float x0, flo
   float g1 = g[i + 1];
   while (i < n - 2 && g1 < x) { ++i; g1 = g[i + 1]; }
   const float g0 = g[i];
-  inv_w = 1.0f / (g1 - g0);
+  inv_w = rcp_(g1 - g0);
   t = (x - g0) * inv_w;
   oob = oob || (x < g[0]) || (x > g[n - 1]) || !(x == x);
   return i;
@@ -542,7 +548,7 @@ CSI_DEV void grid_eval3(const GridDev &gd, const float x[4], float val[4], float
 #pragma unroll
   for (int d = 0; d < 3; ++d) {
     const float g0 = gd.pts[d][idx[d]];
-    iw[d] = 1.0f / (g1[d] - g0);
+    iw[d] = rcp_(g1[d] - g0);
     t[d] = (x[d] - g0) * iw[d];
     oob = oob || (x[d] < gd.pts[d][0]) || (x[d] > gd.pts[d][gd.shape[d] - 1]) || !(x[d] == x[d]);
   }
@@ -608,18 +614,19 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
   float teff = 0.0f;
   if (m.bands > 0) {
     float bcin[4], bcv[4];
-    teff = exp10f(mean[1]);
+    teff = exp2f(mean[1] * kLog2_10);
     bcin[0] = (m.bc_mode == 1) ? teff : mean[1];
     bcin[1] = mean[5]; bcin[2] = st.x[2]; bcin[3] = m.av;
     bc.forward(bcin, bcv);
     float bol = m.bol_mag_sun - 2.5f * mean[4];
-    float dm = 5.0f * (1.0f - log10f(st.dist));
+    const float inv_dist = rcp_(st.dist);
+    float dm = 5.0f * (1.0f - __log2f(st.dist) * 0.30102999566398120f);
 #pragma unroll
     for (int b = 0; b < kMaxBands; ++b)
       if (b < m.bands) mean[7 + b] = (bol - bcv[b]) - dm;
 #pragma unroll
     for (int b = 0; b <= kMaxBands; ++b)
-      if (b == m.bands) mean[7 + b] = 1e3f / st.dist;
+      if (b == m.bands) mean[7 + b] = 1e3f * inv_dist;
   }
   if (mean_out) {
 #pragma unroll
@@ -630,7 +637,7 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
 #pragma unroll
   for (int k = 0; k < kMaxMean; ++k) gm[k] = 0.0f;
   float ll = 0.0f, g_tau = 0.0f;
-  const float inv_tau = 1.0f / st.tau;
+  const float inv_tau = rcp_(st.tau);
   if (m.kind == 0) {
     // Normal(mean[idx], sqrt(var[idx]/tau + diag)).log_prob(obs)   (:231-235)
 #pragma unroll
@@ -638,10 +645,10 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
       if (io.obsm[k] != nullptr) {
         float vk = m.var_ext[k] * inv_tau;
         float s2 = vk + dg_[k];
-        float inv_s2 = 1.0f / s2;
+        float inv_s2 = rcp_(s2);
         float r = ob_[k] - mean[k];
         float q = r * inv_s2;
-        ll += -0.5f * r * q - 0.5f * logf(s2) - kHalfLog2Pi;
+        ll += -0.5f * r * q - 0.5f * log_(s2) - kHalfLog2Pi;
         gm[k] = q;
         float dl_ds2 = 0.5f * (q * q - inv_s2);
         g_tau += dl_ds2 * (-vk * inv_tau);
@@ -727,7 +734,8 @@ CSI_DEV void star_mid(const DevModel &m, const StarIO &io, long long i, StarStat
     gm5 += gin[1];
     g_logmass += gin[1];
     g_mh += gin[2];
-    g_dist = gsum * 5.0f / (st.dist * kLn10) - g_plx * 1e3f / (st.dist * st.dist);
+    const float inv_d = rcp_(st.dist);
+    g_dist = gsum * (5.0f / kLn10) * inv_d - g_plx * 1e3f * inv_d * inv_d;
   }
   st.g_logmass = g_logmass; st.g_mh_dir = g_mh; st.g_dist = g_dist;
   // g_out = g_mean[:7] @ A
