@@ -48,6 +48,11 @@ def parse():
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--nccl-allreduce", action="store_true", help="keep the NCCL allreduce instead of the in-kernel exchange")
     ap.add_argument("--e2e-blocks", type=int, default=6, help="star blocks of the pipelined host-buffer path")
+    ap.add_argument("--e2e-mode", default="zerocopy", choices=["zerocopy", "pipelined"],
+                    help="host-buffer path: the kernel reads / writes pinned host memory itself (one launch), or "
+                         "star blocks with explicit H2D / D2H copies on streams")
+    ap.add_argument("--e2e-equal", action="store_true", help="equal star blocks instead of the triangular ramp")
+    ap.add_argument("--e2e-no-graph", action="store_true", help="issue the host-buffer path per call, no CUDA graph")
     return ap.parse_args()
 
 
@@ -255,24 +260,36 @@ def run_b200(args):
         dist.all_reduce(total, op=dist.ReduceOp.MAX)
     total_ms = float(total.item())
 
-    # ---- end to end: pinned host z -> device -> evaluate -> allreduce -> host, every step ----------------------
-    # The public host-buffer API cuts the local stars into blocks (own handle + stream each) so that the H2D of
-    # block b+1, the kernel of block b and the D2H of block b-1 overlap (parallel.PipelinedHostPotential).
-    from scalable_stellar_inference_b200.parallel import PipelinedHostPotential
-    from scalable_stellar_inference_b200.parallel import block_bounds, shard_bounds, slice_problem
+    # ---- end to end: z in pinned host memory -> evaluate -> gradient and sums in host memory, every step --------
+    # zerocopy (default): the kernel reads the sites from / writes the gradient to pinned host memory itself
+    # (parallel.ZeroCopyHostPotential: one launch, no copy calls, PCIe traffic hidden by the kernel's input staging).
+    # pipelined: the local stars are cut into blocks (own handle + stream each) so that the H2D of block b+1, the
+    # kernel of block b and the D2H of block b-1 overlap (parallel.PipelinedHostPotential).
+    from scalable_stellar_inference_b200.parallel import PipelinedHostPotential, ZeroCopyHostPotential
+    from scalable_stellar_inference_b200.parallel import bind_host_to_device, block_bounds, shard_bounds, slice_problem
     lo_r, hi_r = shard_bounds(args.stars, rank, world)
-    bounds = block_bounds(lo_r, hi_r, max(1, args.e2e_blocks), unit=2 * 128 * model.info()["sm_count"])
-    B = len(bounds)
-    blocks, zb = [], []
-    for b, (lo_b, hi_b) in enumerate(bounds):
-        mb = ssi.HierarchicalStarModel(args.stars, list(OBSERVABLES), bands=BANDS, bc="grid", bc_grid=grid,
-                                       engine=args.engine, device=local)
-        mb.set_shard(rank * B + b, world * B)   # hyper-prior terms on the first block of rank 0 only
-        zl_b, obs_b, diag_b, ml_b, ms_b = slice_problem(z0, obs, diag, ml, ms, lo_b, hi_b)
-        mb.condition(obs_b, diag_b, M_H_loc=ml_b, M_H_scale=ms_b)
-        blocks.append(mb); zb.append(mb.flatten(zl_b))
-    pipe = PipelinedHostPotential(blocks)
-    pipe.load_blocks(zb)
+    prev_affinity = bind_host_to_device(local)   # pinned buffers and the launching thread next to the GPU's PCIe root
+    if args.e2e_mode == "zerocopy":
+        # the device-resident model of this rank (same handle, shard and exchange) fed from host memory
+        pipe = ZeroCopyHostPotential(model)
+        pipe.load(model.flatten(zl))
+        B, bounds = 1, [(lo_r, hi_r)]
+        e2e_api = "parallel.ZeroCopyHostPotential.value_and_grad_host"
+    else:
+        bounds = block_bounds(lo_r, hi_r, max(1, args.e2e_blocks), unit=2 * 128 * model.info()["sm_count"],
+                              ramp=not args.e2e_equal)
+        B = len(bounds)
+        blocks, zb = [], []
+        for b, (lo_b, hi_b) in enumerate(bounds):
+            mb = ssi.HierarchicalStarModel(args.stars, list(OBSERVABLES), bands=BANDS, bc="grid", bc_grid=grid,
+                                           engine=args.engine, device=local)
+            mb.set_shard(rank * B + b, world * B)   # hyper-prior terms on the first block of rank 0 only
+            zl_b, obs_b, diag_b, ml_b, ms_b = slice_problem(z0, obs, diag, ml, ms, lo_b, hi_b)
+            mb.condition(obs_b, diag_b, M_H_loc=ml_b, M_H_scale=ms_b)
+            blocks.append(mb); zb.append(mb.flatten(zl_b))
+        pipe = PipelinedHostPotential(blocks, graph=not args.e2e_no_graph)
+        pipe.load_blocks(zb)
+        e2e_api = "parallel.PipelinedHostPotential.value_and_grad_host"
     for _ in range(2):
         pipe.value_and_grad_host()
     barrier()
@@ -286,8 +303,12 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
     clocks = sampler.stop()
+    if prev_affinity is not None:
+        os.sched_setaffinity(0, prev_affinity)   # the CPU baseline below uses every host core again
     if not (np.isfinite(u_h) and abs(u_h - u_first) <= 1e-7 * abs(u_first)) and not os.environ.get("CSI_TC_DEBUG"):
         raise SystemExit(f"e2e result {u_h} differs from the device-resident result {u_first}")
+    if args.e2e_mode == "zerocopy" and not torch.equal(pot.grad_dev.cpu()[5:], pipe.grad_pin[5:]):
+        raise SystemExit("zero-copy gradient differs from the device-resident gradient")
 
     if rank == 0:
         bf16_peak, hbm_peak, which = measured_peaks()
@@ -306,7 +327,10 @@ def run_b200(args):
             "star_evals_per_s": args.stars * 1e3 / ms_per_step,
             "e2e": {"value": 1e3 / (float(e2e_total.item()) / K), "unit": "evals/s",
                     "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-                    "blocks": B, "api": "parallel.PipelinedHostPotential.value_and_grad_host"},
+                    "blocks": B, "block_stars": [hi_b - lo_b for lo_b, hi_b in bounds],
+                    "host_bound_to_gpu_numa_node": prev_affinity is not None,
+                    "mode": args.e2e_mode, "cuda_graph": getattr(pipe, "graph", None) is not None,
+                    "api": e2e_api},
             "gpu_launches": int(gpu_launches), "gpu_launches_e2e_per_step": B,
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",

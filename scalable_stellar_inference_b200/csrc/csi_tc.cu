@@ -275,6 +275,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   if ((long long)blockIdx.x < n_tiles) my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
   auto slot_iters = [&](int slot) { return (my_tiles + 1 - slot) / 2; };
 
+  // CTA life-cycle marks of the traced CTA: 1 entry, 2 set-up done, 3 all tiles done, 4 reduction done
+  Tracer ctr{(L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ? L.tc.trace + 5 * 1024 : nullptr, 0};
+  ctr.rec(1);
   // ---- one-time setup ----------------------------------------------------------------------------
   for (int i = tid; i < kSmallFloats; i += kThreads) S.small[i] = __ldg(L.tc.small + i);
   for (int i = tid; i < (int)(kResidentBytes / 16); i += kThreads)
@@ -321,6 +324,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   const uint32_t tmem = S.tmem_base;
   const HyperVals hv = S.hv;
   HyperAcc acc{};
+  ctr.rec(2);
 
   if (warp >= 10) {
     // ===== weight loaders: warp 10 + t streams the images of tile slot t, one K-half per slot =============
@@ -457,8 +461,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       if (lane == 0) ptx::mbar_arrive(&S.a_ready[t][c]);
     };
     Tracer tr{nullptr, 0};
-    if (L.tc.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
-      tr.p = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
+    long long *tr_base = nullptr;  // trace of CTA (debug >> 16), starting at this slot's iteration (debug >> 8) & 255
+    if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
+      tr_base = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
     long long it = 0;
     // Start gate: tile B begins a quarter of an evaluation chain after tile A, so that the long CUDA-core phases
     // of one tile (priors; table gather + likelihood; gradient stores) run under the MMA stages of the other.
@@ -492,6 +497,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       const long long tile = (long long)blockIdx.x + (2 * p + t) * gridDim.x;
       const long long i = tile * kTile + row;
       const bool valid = i < n;
+      if (tr_base && p >= ((L.tc.debug >> 8) & 255)) tr.p = tr_base;
       const long long i_next = p + 1 < my_iters ? i + 2LL * kTile * gridDim.x : n;  // same row, this slot's next tile
       StarState st;
       float x[5];
@@ -670,8 +676,10 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   // ---- teardown + reduction (all threads) -----------------------------------------------------------
   ptx::tc_fence_before();
   __syncthreads();
+  ctr.rec(3);
   if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);
   if (MODE == M_POTENTIAL) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper, L.px);
+  ctr.rec(4);
 }
 
 }  // namespace tc

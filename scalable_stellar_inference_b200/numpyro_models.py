@@ -207,9 +207,11 @@ class SingleStarModel:
         process) to rank r's exchange buffer (csi_set_peer_exchange); ``None`` switches it off."""
         if not peer_ptrs:
             _lib.check(self._lib.csi_set_peer_exchange(self._h, 1, 0, None))
+            self._peer_exchange_on = False
             return self
         arr = (C.c_void_p * len(peer_ptrs))(*[C.c_void_p(int(p)) for p in peer_ptrs])
         _lib.check(self._lib.csi_set_peer_exchange(self._h, len(peer_ptrs), self._rank, arr))
+        self._peer_exchange_on = len(peer_ptrs) > 1
         return self
 
     def condition(self, obs, diag=None, M_H_loc=None, M_H_scale=None):

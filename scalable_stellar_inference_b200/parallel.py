@@ -30,22 +30,72 @@ def shard_problem(z: dict, obs, diag, mh_loc, mh_scale, rank: int, world: int):
     return zl, np.asarray(obs)[sl], f(diag), f(mh_loc), f(mh_scale)
 
 
-def block_bounds(lo: int, hi: int, n_blocks: int, unit: int):
+def block_bounds(lo: int, hi: int, n_blocks: int, unit: int, ramp: bool = False):
     """Cut stars [lo, hi) into <= n_blocks contiguous blocks whose sizes are whole multiples of ``unit`` (one full
     round of the persistent kernel: SMs x 2 tiles x 128 stars), remainder last, so that no block pays for a
-    partly filled round."""
+    partly filled round.  ``ramp``: triangular sizes (1, 2, 3, ... 3, 2, 1 in proportion) instead of equal ones --
+    the first H2D and the last D2H of a pipelined evaluation are exposed, so the end blocks are kept small and each
+    block is at most ~2x its neighbour, which keeps the next copy inside the current kernel."""
     n = hi - lo
     units = max(1, -(-n // unit))
     nb = max(1, min(n_blocks, units))
-    base, rem = divmod(units, nb)
+    if ramp:
+        weight = [min(b + 1, nb - b) for b in range(nb)]
+        sizes = [1] * nb
+        for _ in range(units - nb):
+            b = min(range(nb), key=lambda k: (sizes[k] / weight[k], abs(k - (nb - 1) / 2)))
+            sizes[b] += 1
+    else:
+        base, rem = divmod(units, nb)
+        sizes = [base + (1 if b < rem else 0) for b in range(nb)]
+    stars = [k * unit for k in sizes]
+    if ramp:
+        stars[max(range(nb), key=lambda k: sizes[k])] -= units * unit - n  # the partly filled round: a middle block
     out, pos = [], lo
     for b in range(nb):
-        size = (base + (1 if b < rem else 0)) * unit
-        end = min(hi, pos + size)
+        end = min(hi, pos + stars[b])
         if end > pos:
             out.append((pos, end))
         pos = end
     return out
+
+
+def _parse_cpulist(text: str):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def bind_host_to_device(device: int):
+    """Restrict this process to the CPU cores that share a PCIe root / NUMA node with GPU ``device`` (Linux sysfs
+    ``local_cpulist`` of the GPU's PCI function) and return the previous affinity mask, or None when the topology
+    is not visible (containers without sysfs PCI entries) -- then nothing is changed.  Pinned host buffers
+    allocated afterwards are first-touched on that node, so the H2D / D2H copies of the host-buffer path do not
+    cross the socket interconnect; without it the end-to-end rate depends on where the scheduler happened to put
+    the process.  Undo with ``os.sched_setaffinity(0, previous)``."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        index = int(vis.split(",")[device]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else device
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.lower().split(":", 1)
+        with open(f"/sys/bus/pci/devices/{dom[-4:]}:{rest}/local_cpulist") as f:
+            local = _parse_cpulist(f.read())
+        previous = os.sched_getaffinity(0)
+        target = local & previous
+        if not target or target == previous:
+            return None
+        os.sched_setaffinity(0, target)
+        return previous
+    except Exception:  # no NVML / sysfs / affinity support: leave the process where it is
+        return None
 
 
 def slice_problem(z: dict, obs, diag, mh_loc, mh_scale, lo: int, hi: int):
@@ -158,9 +208,13 @@ class PipelinedHostPotential:
     so that the hyper-prior terms are counted once.
     """
 
-    def __init__(self, models, group=None):
+    def __init__(self, models, group=None, graph=True):
         import torch
         self.torch, self.models, self.group = torch, list(models), group
+        # graph: the whole step (every block's copies and kernel, on the blocks' streams) is captured once into a
+        # CUDA graph and replayed with ONE host call per evaluation -- 4 x blocks Python-issued operations per step
+        # otherwise, whose jitter on a busy host shows up directly in the end-to-end rate.
+        self.use_graph, self.graph, self.graph_error = bool(graph), None, None
         self.device = torch.device("cuda", models[0].device)
         self.n_hyper = len(models[0].hyper_sites)
         self.blocks = []
@@ -191,19 +245,51 @@ class PipelinedHostPotential:
         for b, z in zip(self.blocks, z_blocks):
             b["z_pin"].copy_(self.torch.as_tensor(np.asarray(z, np.float32)))
 
-    def value_and_grad_host(self):
-        """Returns (U, dU/dhyper[5], grad_views): per-star gradients are left in the pinned block buffers."""
+    def _issue(self, fork=None):
+        """One evaluation of every block on its own stream; ``fork``: the capturing stream the block streams branch
+        from and join back into (graph capture), None = plain asynchronous issue."""
         torch = self.torch
         for b in self.blocks:
+            if fork is not None:
+                b["stream"].wait_stream(fork)
             with torch.cuda.stream(b["stream"]):
                 b["z_dev"].copy_(b["z_pin"], non_blocking=True)
                 b["model"].potential_device(b["z_dev"].data_ptr(), b["out_dev"].data_ptr(), b["grad_dev"].data_ptr(),
                                             b["stream"].cuda_stream)
                 b["grad_pin"].copy_(b["grad_dev"], non_blocking=True)
                 b["out_pin"].copy_(b["out_dev"], non_blocking=True)
-            self.launches += 1
-        for b in self.blocks:
-            b["stream"].synchronize()
+        if fork is not None:  # join only after every block has branched off, or the blocks would form a chain
+            for b in self.blocks:
+                fork.wait_stream(b["stream"])
+
+    def _capture(self):
+        torch = self.torch
+        try:
+            self._issue()                       # warm: first-use initialisation must not happen under capture
+            torch.cuda.synchronize(self.device)
+            self._graph_stream = torch.cuda.Stream(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=self._graph_stream):
+                self._issue(fork=torch.cuda.current_stream(self.device))
+            self.graph = g
+        except Exception as e:  # capture is an optimisation of the issue path, not of the arithmetic
+            self.graph, self.graph_error, self.use_graph = None, repr(e), False
+            torch.cuda.synchronize(self.device)
+
+    def value_and_grad_host(self):
+        """Returns (U, dU/dhyper[5], grad_views): per-star gradients are left in the pinned block buffers."""
+        torch = self.torch
+        if self.use_graph and self.graph is None:
+            self._capture()
+        if self.graph is not None:
+            with torch.cuda.stream(self._graph_stream):
+                self.graph.replay()
+            self._graph_stream.synchronize()
+        else:
+            self._issue()
+            for b in self.blocks:
+                b["stream"].synchronize()
+        self.launches += len(self.blocks)
         tot = np.sum([b["out_pin"][:6].numpy() for b in self.blocks], axis=0)
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
@@ -211,3 +297,50 @@ class PipelinedHostPotential:
             dist.all_reduce(self._sum, group=self.group)
             tot = self._sum.cpu().numpy()
         return float(tot[0]), tot[1:6].copy(), self.grad_views
+
+
+class ZeroCopyHostPotential:
+    """End-to-end evaluation through HOST buffers with no copy calls at all: the kernel reads the sites straight
+    from pinned host memory and writes the gradient and the 6 sums straight back into it.
+
+    Pinned allocations are device-accessible at their host address (unified virtual addressing), so the host
+    pointers are simply handed to ``csi_potential``.  The tcgen05 kernel fetches a star's sites with asynchronous
+    copies into shared memory half a tile (~15 us) before it needs them and its gradient stores are fire-and-
+    forget, so the PCIe round trips hide under the MMA stages: one launch per evaluation, every input byte crosses
+    the bus once as a coalesced 128-byte read and every gradient byte once as a posted write, and the step costs
+    ~max(kernel, bytes / PCIe rate) with no pipeline fill or drain.  ``z_view[site]`` / ``grad_view[site]`` are
+    numpy views of the pinned buffers for a host-side sampler.  Observations stay resident in HBM (csi_set_data).
+    """
+
+    def __init__(self, model, group=None):
+        import torch
+        self.torch, self.model, self.group = torch, model, group
+        self.device = torch.device("cuda", model.device)
+        n = model.flat_size
+        self.z_pin = torch.zeros(n, dtype=torch.float32).pin_memory()
+        self.grad_pin = torch.zeros(n, dtype=torch.float32).pin_memory()
+        self.out_pin = torch.zeros(8, dtype=torch.float64).pin_memory()
+        self.stream = torch.cuda.Stream(self.device)
+        self.z_view = model.unflatten(self.z_pin.numpy())
+        self.grad_view = model.unflatten(self.grad_pin.numpy())
+        self.h2d_bytes, self.d2h_bytes = n * 4, n * 4 + 6 * 8
+        self.launches = 0
+        self._sum = torch.zeros(6, dtype=torch.float64, device=self.device)
+
+    def load(self, z_flat):
+        self.z_pin.copy_(self.torch.as_tensor(np.asarray(z_flat, np.float32)))
+
+    def value_and_grad_host(self):
+        """Returns (U, dU/dhyper[5], grad_view); the per-star gradients are in the pinned buffer when it returns."""
+        self.model.potential_device(self.z_pin.data_ptr(), self.out_pin.data_ptr(), self.grad_pin.data_ptr(),
+                                    self.stream.cuda_stream)
+        self.launches += 1
+        self.stream.synchronize()
+        tot = self.out_pin[:6].numpy().copy()
+        import torch.distributed as dist
+        fused = getattr(self.model, "_peer_exchange_on", False)
+        if not fused and dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            self._sum.copy_(self.torch.as_tensor(tot))
+            dist.all_reduce(self._sum, group=self.group)
+            tot = self._sum.cpu().numpy()
+        return float(tot[0]), tot[1:6].copy(), self.grad_view

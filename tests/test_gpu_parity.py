@@ -183,3 +183,27 @@ def test_pipelined_host_blocks_reproduce_single_handle():
     for site in spec.star_sites():
         cat = np.concatenate([gv[site] for gv in gviews])
         assert np.array_equal(cat, g_full[site]), site
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("engine", ["tcgen05", "ffma"])
+def test_zero_copy_host_potential_is_bit_identical_to_device_buffers(engine):
+    """parallel.ZeroCopyHostPotential: the kernel reading z from / writing the gradient to pinned host memory gives
+    exactly what it gives with device buffers (several evaluations: the staging column is reused across tiles)."""
+    from scalable_stellar_inference_b200.parallel import ZeroCopyHostPotential
+    name, n = "hier_phot_grid", 40_000 if engine == "tcgen05" else 3000
+    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, 1000)
+    rep = n // 1000
+    tile = lambda a: np.tile(np.asarray(a), (rep,) + (1,) * (np.ndim(a) - 1))  # noqa: E731
+    zb = {k: (v if np.ndim(v) == 0 else tile(v)) for k, v in z0.items()}
+    model = PU.product_model(name, n, engine).condition(tile(obs), tile(diag), M_H_loc=tile(ml), M_H_scale=tile(ms))
+    zf = model.flatten(zb)
+    out, grad = model.potential_and_grad_flat(zf)
+    zc = ZeroCopyHostPotential(model)
+    zc.load(zf)
+    for _ in range(3):
+        zc.grad_pin.zero_()
+        u, gh, gview = zc.value_and_grad_host()
+        assert u == out[0] and np.array_equal(gh, out[1:6])
+        assert np.array_equal(zc.grad_pin.numpy()[5:], np.asarray(grad)[5:])
+    assert zc.h2d_bytes == zf.size * 4 and zc.launches == 3

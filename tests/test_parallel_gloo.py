@@ -104,3 +104,16 @@ def test_block_bounds_are_round_aligned_and_cover_the_range():
         assert b[0][0] == lo and b[-1][1] == hi and len(b) <= nb
         assert all(x[1] == y[0] for x, y in zip(b, b[1:]))
         assert all((e - s) % unit == 0 for s, e in b[:-1])          # only the last block may be partial
+
+
+def test_ramped_block_bounds_cover_the_range_with_small_end_blocks():
+    from scalable_stellar_inference_b200.parallel import block_bounds
+    unit = 2 * 128 * 148
+    for lo, hi, nb in ((0, 1_000_000, 6), (0, 1_000_000, 8), (500_000, 1_000_000, 4), (0, 700, 6), (3, 3 + unit, 5)):
+        b = block_bounds(lo, hi, nb, unit, ramp=True)
+        assert b[0][0] == lo and b[-1][1] == hi and len(b) <= nb
+        assert all(x[1] == y[0] and x[1] > x[0] for x, y in zip(b, b[1:]))
+        sizes = [e - s for s, e in b]
+        assert sum(1 for k in sizes if k % unit) <= 1                 # one partly filled round at most
+        if len(b) >= 4:
+            assert sizes[0] < max(sizes) and sizes[-1] < max(sizes)   # the exposed copies belong to small blocks
