@@ -274,7 +274,7 @@ def run_b200(args):
         pipe = ZeroCopyHostPotential(model)
         pipe.load(model.flatten(zl))
         B, bounds = 1, [(lo_r, hi_r)]
-        e2e_api = "parallel.ZeroCopyHostPotential.value_and_grad_host"
+        e2e_api = "csi_potential_host on page-locked buffers (parallel.ZeroCopyHostPotential.value_and_grad_host)"
     else:
         bounds = block_bounds(lo_r, hi_r, max(1, args.e2e_blocks), unit=2 * 128 * model.info()["sm_count"],
                               ramp=not args.e2e_equal)

@@ -146,8 +146,9 @@ int csi_layout(const csi_handle *h, int32_t *n_hyper, int32_t *n_star_sites, con
  * Stream-ordered, no host synchronisation, no allocation. `stream` is a cudaStream_t (NULL = legacy default). */
 int csi_potential(csi_handle *h, const float *z_dev, double *out_dev, float *grad_dev, void *stream);
 
-/* Same through HOST buffers (pinned staging inside the handle): H2D of z, evaluate, D2H of out+grad,
- * synchronise.  This is the end-to-end call timed as `e2e` in bench.py. */
+/* Same through HOST buffers, synchronous.  Page-locked (cudaHostAlloc / cudaHostRegister) z_host / grad_host are
+ * accessed by the kernel itself over PCIe -- no copy calls, one launch; pageable ones go through pinned staging
+ * inside the handle (H2D of z, evaluate, D2H of grad).  This is the end-to-end call timed as `e2e` in bench.py. */
 int csi_potential_host(csi_handle *h, const float *z_host, double *out_host, float *grad_host);
 
 /* Emulator plug point: replaces Emulator.model (src/celestify/_jax/emulator.py:35-50) and the VJP JAX

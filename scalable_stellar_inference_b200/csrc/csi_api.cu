@@ -520,19 +520,39 @@ extern "C" int csi_potential(csi_handle *h, const float *z_dev, double *out_dev,
   return CSI_OK;
 }
 
+// device-visible alias of a pinned / registered host pointer (unified addressing), or null for pageable memory
+static void *device_alias_of_host(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
 extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *out_host, float *grad_host) {
   if (!h || !z_host || !out_host || !grad_host) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
   CK(cudaSetDevice(h->device));
   const size_t bytes = (size_t)h->stage_len * sizeof(float);
-  memcpy(h->h_z, z_host, bytes);
-  CK(cudaMemcpyAsync(h->d_z, h->h_z, bytes, cudaMemcpyHostToDevice, h->stream));
-  int rc = csi_potential(h, h->d_z, h->d_out, h->d_grad, h->stream);
+  // Page-locked caller buffers are read / written by the kernel itself over PCIe (its input staging runs half a
+  // tile ahead, gradient stores are posted writes): no copy calls, one launch.  Pageable buffers go through the
+  // handle's pinned staging area.
+  const float *z_alias = static_cast<const float *>(device_alias_of_host(z_host));
+  float *grad_alias = static_cast<float *>(device_alias_of_host(grad_host));
+  const float *z_in = z_alias;
+  if (!z_alias) {
+    memcpy(h->h_z, z_host, bytes);
+    CK(cudaMemcpyAsync(h->d_z, h->h_z, bytes, cudaMemcpyHostToDevice, h->stream));
+    z_in = h->d_z;
+  }
+  double *out_alias = static_cast<double *>(device_alias_of_host(h->h_out));
+  int rc = csi_potential(h, z_in, out_alias ? out_alias : h->d_out, grad_alias ? grad_alias : h->d_grad, h->stream);
   if (rc != CSI_OK) return rc;
-  CK(cudaMemcpyAsync(h->h_grad, h->d_grad, bytes, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(h->h_out, h->d_out, 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (!grad_alias) CK(cudaMemcpyAsync(h->h_grad, h->d_grad, bytes, cudaMemcpyDeviceToHost, h->stream));
+  if (!out_alias) CK(cudaMemcpyAsync(h->h_out, h->d_out, 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  memcpy(grad_host, h->h_grad, bytes);
+  if (!grad_alias) memcpy(grad_host, h->h_grad, bytes);
   memcpy(out_host, h->h_out, 6 * sizeof(double));
   return CSI_OK;
 }

@@ -279,6 +279,11 @@ class SingleStarModel:
         """Device pointers (e.g. ``torch.Tensor.data_ptr()``), stream-ordered, no synchronisation."""
         _lib.check(self._lib.csi_potential(self._h, z_ptr, out_ptr, grad_ptr, stream or None))
 
+    def potential_host(self, z_ptr: int, out_ptr: int, grad_ptr: int):
+        """Host pointers, synchronous (csi_potential_host).  Page-locked z / gradient buffers (e.g. pinned torch
+        tensors) are read and written by the kernel itself -- no copies; pageable ones are staged."""
+        _lib.check(self._lib.csi_potential_host(self._h, z_ptr, out_ptr, grad_ptr))
+
     def time_potential(self, z_ptr: int, out_ptr: int, grad_ptr: int, iters: int) -> float:
         ms = C.c_float()
         _lib.check(self._lib.csi_time_potential(self._h, z_ptr, out_ptr, grad_ptr, iters, C.byref(ms)))

@@ -303,8 +303,8 @@ class ZeroCopyHostPotential:
     """End-to-end evaluation through HOST buffers with no copy calls at all: the kernel reads the sites straight
     from pinned host memory and writes the gradient and the 6 sums straight back into it.
 
-    Pinned allocations are device-accessible at their host address (unified virtual addressing), so the host
-    pointers are simply handed to ``csi_potential``.  The tcgen05 kernel fetches a star's sites with asynchronous
+    Pinned allocations are device-accessible (unified virtual addressing); ``csi_potential_host`` -- the C ABI's
+    host-buffer call -- recognises page-locked buffers and launches the kernel on them.  The tcgen05 kernel fetches a star's sites with asynchronous
     copies into shared memory half a tile (~15 us) before it needs them and its gradient stores are fire-and-
     forget, so the PCIe round trips hide under the MMA stages: one launch per evaluation, every input byte crosses
     the bus once as a coalesced 128-byte read and every gradient byte once as a posted write, and the step costs
@@ -319,8 +319,7 @@ class ZeroCopyHostPotential:
         n = model.flat_size
         self.z_pin = torch.zeros(n, dtype=torch.float32).pin_memory()
         self.grad_pin = torch.zeros(n, dtype=torch.float32).pin_memory()
-        self.out_pin = torch.zeros(8, dtype=torch.float64).pin_memory()
-        self.stream = torch.cuda.Stream(self.device)
+        self.out = np.zeros(8, np.float64)
         self.z_view = model.unflatten(self.z_pin.numpy())
         self.grad_view = model.unflatten(self.grad_pin.numpy())
         self.h2d_bytes, self.d2h_bytes = n * 4, n * 4 + 6 * 8
@@ -332,11 +331,9 @@ class ZeroCopyHostPotential:
 
     def value_and_grad_host(self):
         """Returns (U, dU/dhyper[5], grad_view); the per-star gradients are in the pinned buffer when it returns."""
-        self.model.potential_device(self.z_pin.data_ptr(), self.out_pin.data_ptr(), self.grad_pin.data_ptr(),
-                                    self.stream.cuda_stream)
+        self.model.potential_host(self.z_pin.data_ptr(), self.out.ctypes.data, self.grad_pin.data_ptr())
         self.launches += 1
-        self.stream.synchronize()
-        tot = self.out_pin[:6].numpy().copy()
+        tot = self.out[:6].copy()
         import torch.distributed as dist
         fused = getattr(self.model, "_peer_exchange_on", False)
         if not fused and dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
