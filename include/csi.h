@@ -181,6 +181,26 @@ int csi_synchronize(csi_handle *h);
  * csi_potential, [3]=n_local, [4]=dynamic shared memory of the potential kernel, [5]=grid size. */
 int csi_info(const csi_handle *h, int64_t info[8]);
 
+/* ---- NUTS vector arithmetic around csi_potential (the caller of the path) ------------------------
+ * One leapfrog of numpyro's velocity-Verlet (numpyro/infer/hmc_util.py velocity_verlet, driven from
+ * scripts/model_star.py:134-152) is  csi_leapfrog_pre -> csi_potential(z1) [-> allreduce of out6] ->
+ * csi_leapfrog_post; all vectors are float[n_hyper + n_sites*n_local] in csi_layout order, device memory,
+ * stream-ordered, no synchronisation.
+ *   pre : r_half = r - eps/2 g ;  z1 = z + eps inv_mass r_half ;  zeroes kin2
+ *   post: g1 = grad with the hyper slots taken from out6[1..] (the REDUCED sums) ;  r1 = r_half - eps/2 g1 ;
+ *         kin2[0] = sum over local stars of inv_mass r1^2 (allreduce this when sharded), kin2[1] = the hyper part;
+ *         kinetic energy = (kin2[0] + kin2[1]) / 2. */
+int csi_leapfrog_pre(csi_handle *h, const float *z, const float *r, const float *g, const float *inv_mass,
+                     float eps, float *z1, float *r_half, double *kin2, void *stream);
+int csi_leapfrog_post(csi_handle *h, const float *r_half, const float *grad, const double *out6,
+                      const float *inv_mass, float eps, float *r1, float *g1, double *kin2, void *stream);
+
+/* Generalised U-turn test (hmc_util._is_turning): rc = r_sum - (r_left + r_right)/2;
+ * dots4 = [(inv_mass r_left).rc, (inv_mass r_right).rc] over the local stars (allreduce when sharded), then the
+ * same two over the hyper entries; turning iff dots4[0]+dots4[2] <= 0 or dots4[1]+dots4[3] <= 0. */
+int csi_uturn(csi_handle *h, const float *r_left, const float *r_right, const float *r_sum, const float *inv_mass,
+              double *dots4, void *stream);
+
 /* Times `iters` back-to-back csi_potential calls on the handle's own stream with CUDA events recorded on
  * that stream; returns the mean milliseconds per call.  Used by bench.py for the roofline numbers. */
 int csi_time_potential(csi_handle *h, const float *z_dev, double *out_dev, float *grad_dev, int32_t iters,

@@ -70,6 +70,9 @@ _PROTOS = {
     "csi_layout": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p)]),
     "csi_potential": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "csi_potential_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "csi_leapfrog_pre": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
+    "csi_leapfrog_post": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
+    "csi_uturn": (C.c_int, [C.c_void_p] * 7),
     "csi_net_forward": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "csi_net_vjp": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "csi_grid_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

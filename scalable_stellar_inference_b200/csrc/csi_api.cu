@@ -697,3 +697,5 @@ extern "C" int csi_time_potential(csi_handle *h, const float *z_dev, double *out
   *ms_per_call = ms / iters;
   return CSI_OK;
 }
+
+#include "csi_nuts.cuh"  // NUTS leapfrog / U-turn vector kernels (csi_leapfrog_pre, csi_leapfrog_post, csi_uturn)

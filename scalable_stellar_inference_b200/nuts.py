@@ -22,6 +22,11 @@ import numpy as np
 import torch
 
 
+def _check(rc):
+    from . import _lib
+    _lib.check(rc)
+
+
 class VectorSpace:
     """Inner products of ``[hyper | local stars]`` vectors; ``group`` = torch.distributed group or None."""
 
@@ -106,14 +111,22 @@ class NUTS:
 
     def _is_turning(self, r_left, r_right, r_sum):
         # numpyro / Stan generalised criterion on the summed momentum (end points counted half)
+        if hasattr(self.potential, "uturn"):
+            a, b = self.potential.uturn(r_left, r_right, r_sum, self.inv_mass)
+            return a <= 0.0 or b <= 0.0
         rc = r_sum - 0.5 * (r_left + r_right)
         a, b = self.space.dots([(self.inv_mass * r_left, rc), (self.inv_mass * r_right, rc)])
         return a <= 0.0 or b <= 0.0
 
     # ---- tree ------------------------------------------------------------------------------------------------
     def _base(self, z, r, g, eps, h0):
-        z1, r1, u1, g1 = self._leapfrog(z, r, g, eps)
-        h1 = u1 + self._kinetic(r1)
+        if hasattr(self.potential, "leapfrog"):   # fused vector kernels around the potential: one host sync
+            self.n_evals += 1
+            z1, r1, g1, u1, k1 = self.potential.leapfrog(z, r, g, eps, self.inv_mass)
+            h1 = u1 + k1
+        else:
+            z1, r1, u1, g1 = self._leapfrog(z, r, g, eps)
+            h1 = u1 + self._kinetic(r1)
         de = h1 - h0
         if not math.isfinite(de):
             de = math.inf
@@ -301,6 +314,7 @@ class DevicePotential:
         from .parallel import ShardedPotential
         self.sp = ShardedPotential(model, group)
         self.model, self.nh = model, len(model.hyper_sites)
+        self._scratch = self._dots_dev = self._dots_pin = None
 
     def __call__(self, z):
         sp = self.sp
@@ -309,6 +323,51 @@ class DevicePotential:
         if self.nh:
             g[: self.nh] = out[1: 1 + self.nh].to(g.dtype)
         return float(out[0].item()), g
+
+    # ---- the leapfrog and the U-turn test as three libcsi vector kernels (csi_leapfrog_pre / _post, csi_uturn) ----
+    def _sharded(self):
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size(self.sp.group) > 1
+
+    def leapfrog(self, z, r, g, eps, inv_mass):
+        """One velocity-Verlet step: returns (z1, r1, g1, U(z1), kinetic(r1)) with ONE host synchronisation.
+        pre-kernel -> potential kernel (-> allreduce of the 6 sums unless fused) -> post-kernel -> 8 doubles D2H."""
+        sp, lib, h = self.sp, self.model._lib, self.model._h
+        if self._scratch is None or self._scratch.shape != z.shape:
+            self._scratch = torch.empty_like(z)
+        z1, r1, g1 = torch.empty_like(z), torch.empty_like(z), torch.empty_like(z)
+        stream = torch.cuda.current_stream(z.device)
+        kin = sp.out_dev[6:8]
+        _check(lib.csi_leapfrog_pre(h, z.data_ptr(), r.data_ptr(), g.data_ptr(), inv_mass.data_ptr(), float(eps),
+                                    z1.data_ptr(), self._scratch.data_ptr(), kin.data_ptr(), stream.cuda_stream))
+        out, grad = sp.value_and_grad_device(z1)
+        _check(lib.csi_leapfrog_post(h, self._scratch.data_ptr(), grad.data_ptr(), out.data_ptr(),
+                                     inv_mass.data_ptr(), float(eps), r1.data_ptr(), g1.data_ptr(), kin.data_ptr(),
+                                     stream.cuda_stream))
+        if self._sharded():
+            import torch.distributed as dist
+            dist.all_reduce(sp.out_dev[6:7], group=sp.group)
+        sp.out_pin.copy_(sp.out_dev, non_blocking=True)
+        stream.synchronize()
+        o = sp.out_pin
+        return z1, r1, g1, float(o[0]), 0.5 * (float(o[6]) + float(o[7]))
+
+    def uturn(self, r_left, r_right, r_sum, inv_mass):
+        """The two inner products of the generalised U-turn criterion, one kernel + one host synchronisation."""
+        lib, h = self.model._lib, self.model._h
+        stream = torch.cuda.current_stream(r_sum.device)
+        if self._dots_dev is None:
+            self._dots_dev = torch.zeros(4, dtype=torch.float64, device=r_sum.device)
+            self._dots_pin = torch.zeros(4, dtype=torch.float64).pin_memory()
+        _check(lib.csi_uturn(h, r_left.data_ptr(), r_right.data_ptr(), r_sum.data_ptr(), inv_mass.data_ptr(),
+                             self._dots_dev.data_ptr(), stream.cuda_stream))
+        if self._sharded():
+            import torch.distributed as dist
+            dist.all_reduce(self._dots_dev[0:2], group=self.sp.group)
+        self._dots_pin.copy_(self._dots_dev, non_blocking=True)
+        stream.synchronize()
+        d = self._dots_pin
+        return float(d[0]) + float(d[2]), float(d[1]) + float(d[3])
 
 
 def sample_model(model, z0_flat, num_warmup, num_samples, seed=0, group=None, rank=0, world=1, collect=None, **kw):

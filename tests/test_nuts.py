@@ -90,3 +90,42 @@ def test_posterior_of_cuda_potential_matches_oracle_potential():
         assert 0.4 < a[:, k].std() / b[:, k].std() < 2.5
     assert bad <= 1
     assert sum(out_gpu["diverging"]) <= 0.1 * ns
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,n", [("hier_phot_grid", 3000), ("multi_informative", 64)])
+def test_fused_leapfrog_and_uturn_kernels_match_the_vector_ops(name, n):
+    """csi_leapfrog_pre / csi_leapfrog_post / csi_uturn == the same step written with torch ops around the potential
+    (velocity-Verlet and the generalised U-turn dots), for a model with and one without hyper-parameters."""
+    from scalable_stellar_inference_b200.nuts import DevicePotential
+    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, n)
+    model = PU.product_model(name, n, "tcgen05").condition(obs, diag, M_H_loc=ml, M_H_scale=ms)
+    dev = torch.device("cuda", model.device)
+    pot = DevicePotential(model)
+    nh = pot.nh
+    gen = torch.Generator(device=dev).manual_seed(3)
+    z = torch.as_tensor(model.flatten(z0), device=dev)
+    r = torch.randn(z.shape, generator=gen, device=dev)
+    im = torch.rand(z.shape, generator=gen, device=dev) + 0.5
+    u0, g0 = pot(z)
+    for eps in (1e-3, -2e-3):
+        # reference: torch ops
+        rh = r - (0.5 * eps) * g0
+        z1_ref = z + eps * (im * rh)
+        u1_ref, g1_ref = pot(z1_ref)
+        r1_ref = rh - (0.5 * eps) * g1_ref
+        k_ref = 0.5 * float(torch.dot((im * r1_ref).double(), r1_ref.double()))
+        z1, r1, g1, u1, k1 = pot.leapfrog(z, r, g0, eps, im)
+        assert torch.allclose(z1, z1_ref, rtol=0, atol=1e-6 * float(z1_ref.abs().max()))
+        assert u1 == pytest.approx(u1_ref, rel=1e-6)   # z1 differs by an ulp (fused multiply-add), U is steep
+        assert torch.allclose(g1, g1_ref, rtol=1e-5, atol=1e-5 * float(g1_ref.abs().max()))
+        assert torch.allclose(r1, r1_ref, rtol=1e-5, atol=1e-5 * float(r1_ref.abs().max()))
+        assert k1 == pytest.approx(k_ref, rel=1e-6)
+        if nh:   # hyper slots of the returned gradient are the reduced sums, not the fp32 local partials
+            assert torch.equal(g1[:nh], pot.sp.out_dev[1:1 + nh].float())
+    r_left, r_right = r, torch.randn(z.shape, generator=gen, device=dev)
+    r_sum = r_left + r_right + torch.randn(z.shape, generator=gen, device=dev)
+    rc = (r_sum - 0.5 * (r_left + r_right)).double()
+    a_ref = float(torch.dot((im * r_left).double(), rc)); b_ref = float(torch.dot((im * r_right).double(), rc))
+    a, b = pot.uturn(r_left, r_right, r_sum, im)
+    assert a == pytest.approx(a_ref, rel=1e-6, abs=1e-6 * n) and b == pytest.approx(b_ref, rel=1e-6, abs=1e-6 * n)
