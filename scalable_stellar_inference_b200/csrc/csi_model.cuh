@@ -294,12 +294,43 @@ CSI_DEV void star_load_z(const DevModel &m, const StarIO &io, long long i, StarI
 // pending, then rows k / kMaxMean + k the observation / extra variance of mean k until star_mid has read them.
 constexpr int kStageRows = 2 * kMaxMean;
 constexpr int kStageStride = 256;  // one column per epilogue thread
+// (all rows are read unconditionally -- independent LDS in one basic block -- and absent inputs are replaced by
+// a select afterwards: a never-written row may hold any bit pattern, a select does not propagate it)
 CSI_DEV void star_take_z(const DevModel &m, const StarIO &io, const float *col, StarIn &in) {
+  float v[kSlots + 3];
 #pragma unroll
-  for (int s = 0; s < kSlots; ++s) in.zv[s] = io.z[s] ? col[s * kStageStride] : 0.0f;
-  in.mloc = io.mh_loc ? col[9 * kStageStride] : m.mh.loc;
-  in.mscale = io.mh_scale ? col[10 * kStageStride] : m.mh.inv_scale;
-  in.mlogz = io.mh_logz ? col[11 * kStageStride] : m.mh.lognorm;
+  for (int s = 0; s < kSlots + 3; ++s) v[s] = col[s * kStageStride];
+#pragma unroll
+  for (int s = 0; s < kSlots; ++s) in.zv[s] = io.z[s] ? v[s] : 0.0f;
+  in.mloc = io.mh_loc ? v[9] : m.mh.loc;
+  in.mscale = io.mh_scale ? v[10] : m.mh.inv_scale;
+  in.mlogz = io.mh_logz ? v[11] : m.mh.lognorm;
+}
+
+// the arrays a tile copies into its staging column: global base pointer (star 0) and row, built once per CTA
+struct StageList {
+  const float *src[kStageRows];
+  int row[kStageRows];
+  int n;
+};
+CSI_DEV void stage_list_sites(const StarIO &io, StageList &l) {
+  int c = 0;
+  for (int s = 0; s < kSlots; ++s)
+    if (io.z[s]) { l.src[c] = io.z[s]; l.row[c++] = s; }
+  if (io.mh_loc) { l.src[c] = io.mh_loc; l.row[c++] = 9; }
+  if (io.mh_scale) { l.src[c] = io.mh_scale; l.row[c++] = 10; }
+  if (io.mh_logz) { l.src[c] = io.mh_logz; l.row[c++] = 11; }
+  l.n = c;
+}
+CSI_DEV void stage_list_obs(const DevModel &m, const StarIO &io, StageList &l) {
+  int c = 0;
+  if (m.kind == 0)
+    for (int k = 0; k < kMaxMean; ++k)
+      if (io.obsm[k]) {
+        l.src[c] = io.obsm[k]; l.row[c++] = k;
+        if (io.diagm[k]) { l.src[c] = io.diagm[k]; l.row[c++] = kMaxMean + k; }
+      }
+  l.n = c;
 }
 
 CSI_DEV void star_pre(const DevModel &m, const HyperVals &h, const StarIn &in, StarState &st, HyperAcc &acc) {
@@ -588,11 +619,14 @@ CSI_DEV void star_load_obs(const DevModel &m, const StarIO &io, long long i, Sta
 }
 
 CSI_DEV void star_take_obs(const DevModel &m, const StarIO &io, const float *col, StarObs &so) {
+  float v[kStageRows];
+#pragma unroll
+  for (int k = 0; k < kStageRows; ++k) v[k] = col[k * kStageStride];
 #pragma unroll
   for (int k = 0; k < kMaxMean; ++k) {
     const bool on = m.kind == 0 && io.obsm[k] != nullptr;
-    so.ob[k] = on ? col[k * kStageStride] : 0.0f;
-    so.dg[k] = (on && io.diagm[k]) ? col[(kMaxMean + k) * kStageStride] : 0.0f;
+    so.ob[k] = on ? v[k] : 0.0f;
+    so.dg[k] = (on && io.diagm[k]) ? v[kMaxMean + k] : 0.0f;
   }
 }
 

@@ -89,6 +89,7 @@ struct __align__(128) Smem {
   float small[kSmallFloats];
   uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
   float stage[kStageRows][kStageStride];  // per-thread input staging column (star_take_z / star_take_obs)
+  StageList sites_list, obs_list;         // which arrays go into the column (built once, uniform copy loops)
   float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
   unsigned short grid_lut[4][kLutBins];
   uint64_t w_full[2][2], w_empty[2][2], a_ready[2][2], d_ready[2], start_b;  // a_ready: one barrier per K-half
@@ -317,6 +318,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
     S.hv = h;
   }
+  if (!NET && tid == 32) { stage_list_sites(io, S.sites_list); stage_list_obs(m, io, S.obs_list); }
   if (warp == 8) ptx::tmem_alloc<kTmemCols>(&S.tmem_base);
   ptx::tc_fence_before();
   __syncthreads();
@@ -473,24 +475,14 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     // observations out of the column, the observations of tile p once its priors have taken the sites.  Nothing
     // but the thread itself touches the column, so cp.async.wait_all is the only synchronisation.
     float *col = &S.stage[0][tid];
-    auto stage_sites = [&](long long ii) {
+    auto stage = [&](const StageList &l, long long ii) {
       if (NET || ii >= n) return;
-#pragma unroll
-      for (int sl = 0; sl < kSlots; ++sl)
-        if (io.z[sl]) ptx::cp_async4(col + sl * kStageStride, io.z[sl] + ii);
-      if (io.mh_loc) ptx::cp_async4(col + 9 * kStageStride, io.mh_loc + ii);
-      if (io.mh_scale) ptx::cp_async4(col + 10 * kStageStride, io.mh_scale + ii);
-      if (io.mh_logz) ptx::cp_async4(col + 11 * kStageStride, io.mh_logz + ii);
+      const int cnt = l.n;
+#pragma unroll 4
+      for (int j = 0; j < cnt; ++j) ptx::cp_async4(col + l.row[j] * kStageStride, l.src[j] + ii);
     };
-    auto stage_obs = [&](long long ii) {
-      if (NET || ii >= n || m.kind != 0) return;
-#pragma unroll
-      for (int k = 0; k < kMaxMean; ++k)
-        if (io.obsm[k]) {
-          ptx::cp_async4(col + k * kStageStride, io.obsm[k] + ii);
-          if (io.diagm[k]) ptx::cp_async4(col + (kMaxMean + k) * kStageStride, io.diagm[k] + ii);
-        }
-    };
+    auto stage_sites = [&](long long ii) { stage(S.sites_list, ii); };
+    auto stage_obs = [&](long long ii) { stage(S.obs_list, ii); };
     if (my_iters > 0) stage_sites(((long long)blockIdx.x + t * gridDim.x) * kTile + row);
     if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
     for (long long p = 0; p < my_iters; ++p) {
@@ -543,7 +535,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         for (int q = 9; q < 16; ++q) a0[q] = 0u;
         ptx::tmem_st16(t_base + (uint32_t)(((it & 1) ^ 1) * 128), a0);  // A of stage `it` lives in the other region
       }
+      tr.rec(504);
       publish_a(0);
+      tr.rec(505);
       if (!(L.tc.debug & 2)) stage_obs(i);  // the column is free: the priors hold the sites in registers
 
       float un = 1.0f;    // cotangent un-scaling: true value = D * un
@@ -587,6 +581,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             StarObs so;
             tr.rec(601);
             ptx::cp_async_wait_all();
+            tr.rec(611);
             star_take_obs(m, io, col, so);
             if (tr.p) {
               uint32_t x_ = 0;
