@@ -280,30 +280,33 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   Tracer ctr{(L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ? L.tc.trace + 5 * 1024 : nullptr, 0};
   ctr.rec(1);
   // ---- one-time setup ----------------------------------------------------------------------------
-  for (int i = tid; i < kSmallFloats; i += kThreads) S.small[i] = __ldg(L.tc.small + i);
-  for (int i = tid; i < (int)(kResidentBytes / 16); i += kThreads)
-    reinterpret_cast<uint4 *>(S.resident)[i] = __ldg(reinterpret_cast<const uint4 *>(L.tc.resident) + i);
-  const uint32_t ca16 = (uint32_t)__half_as_ushort(__float2half_rn(__ldg(L.tc.small + oBiasA)));
-  if (tid < 128) {
-    // constant A tile of the bias MMA, K-major core-matrix layout: row tid, k = 0..2 -> c_A, k = 3..15 -> 0
-    uint4 *row = reinterpret_cast<uint4 *>(S.a_const + (tid >> 3) * kSbo + (tid & 7) * 16);
-    row[0] = make_uint4(ca16 | (ca16 << 16), ca16, 0u, 0u);
-    row[kLbo / 16] = make_uint4(0u, 0u, 0u, 0u);
-  }
+  // Warp 11 initialises the barriers and evaluates the hyper-parameter terms (a ~3 k-cycle dependent chain behind
+  // a cold global load) while warps 0..10 copy the resident operands, so the two run side by side.
+  constexpr int kCopyThreads = kThreads - 32;
   GridDev gl = L.grid;
-  if (BC == 1 && gl.shape[0] + gl.shape[1] + gl.shape[2] + gl.shape[3] <= kGridPtsMax) {
-    int off = 0;
-#pragma unroll
-    for (int d = 0; d < 4; ++d) {
-      for (int i = tid; i < gl.shape[d]; i += kThreads) S.grid_pts[off + i] = L.grid.pts[d][i];
-      for (int i = tid; i < kLutBins; i += kThreads) S.grid_lut[d][i] = L.grid.lut[d][i];
-      gl.pts[d] = S.grid_pts + off;
-      gl.lut[d] = S.grid_lut[d];
-      off += gl.shape[d];
+  const bool grid_in_smem = BC == 1 && gl.shape[0] + gl.shape[1] + gl.shape[2] + gl.shape[3] <= kGridPtsMax;
+  const uint32_t ca16 = (uint32_t)__half_as_ushort(__float2half_rn(__ldg(L.tc.small + oBiasA)));
+  if (tid < kCopyThreads) {
+    for (int i = tid; i < kSmallFloats; i += kCopyThreads) S.small[i] = __ldg(L.tc.small + i);
+    for (int i = tid; i < (int)(kResidentBytes / 16); i += kCopyThreads)
+      reinterpret_cast<uint4 *>(S.resident)[i] = __ldg(reinterpret_cast<const uint4 *>(L.tc.resident) + i);
+    if (tid < 128) {
+      // constant A tile of the bias MMA, K-major core-matrix layout: row tid, k = 0..2 -> c_A, k = 3..15 -> 0
+      uint4 *row = reinterpret_cast<uint4 *>(S.a_const + (tid >> 3) * kSbo + (tid & 7) * 16);
+      row[0] = make_uint4(ca16 | (ca16 << 16), ca16, 0u, 0u);
+      row[kLbo / 16] = make_uint4(0u, 0u, 0u, 0u);
     }
-  }
-  ptx::fence_proxy_async_smem();  // generic-proxy writes above are read by tcgen05.mma (async proxy)
-  if (tid == 0) {
+    if (grid_in_smem) {
+      int off = 0;
+#pragma unroll
+      for (int d = 0; d < 4; ++d) {
+        for (int i = tid; i < gl.shape[d]; i += kCopyThreads) S.grid_pts[off + i] = L.grid.pts[d][i];
+        for (int i = tid; i < kLutBins; i += kCopyThreads) S.grid_lut[d][i] = L.grid.lut[d][i];
+        off += gl.shape[d];
+      }
+    }
+    if (!NET && tid == 32) { stage_list_sites(io, S.sites_list); stage_list_obs(m, io, S.obs_list); }
+  } else if (tid == kCopyThreads) {
     for (int b = 0; b < 2; ++b) {
       for (int hh = 0; hh < 2; ++hh) {
         ptx::mbar_init(&S.w_full[b][hh], 1);
@@ -318,7 +321,16 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
     S.hv = h;
   }
-  if (!NET && tid == 32) { stage_list_sites(io, S.sites_list); stage_list_obs(m, io, S.obs_list); }
+  if (grid_in_smem) {
+    int off = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      gl.pts[d] = S.grid_pts + off;
+      gl.lut[d] = S.grid_lut[d];
+      off += gl.shape[d];
+    }
+  }
+  ptx::fence_proxy_async_smem();  // generic-proxy writes above are read by tcgen05.mma (async proxy)
   if (warp == 8) ptx::tmem_alloc<kTmemCols>(&S.tmem_base);
   ptx::tc_fence_before();
   __syncthreads();
