@@ -241,11 +241,16 @@ __device__ __forceinline__ void issue_half(uint32_t d, uint32_t a_reg, uint32_t 
 }
 
 // clock64 trace (CSI_TC_DEBUG & 8): recorder `who` of CTA 0 appends (tag, clock) pairs to its 1024-entry region
+// clock64 trace (CSI_TC_DEBUG=8).  The marks cost ~3.5 % of the kernel even when idle (a predicated store pair
+// and a counter per mark), so they exist only in the TRACE instantiation, which csi_tc_trace launches select.
+template <bool ON>
 struct Tracer {
   long long *p;
   int n;
   __device__ __forceinline__ void rec(int tag) {
-    if (p != nullptr && n < 510) { p[2 * n] = tag; p[2 * n + 1] = clock64(); ++n; }
+    if constexpr (ON) {
+      if (p != nullptr && n < 510) { p[2 * n] = tag; p[2 * n + 1] = clock64(); ++n; }
+    }
   }
 };
 
@@ -255,7 +260,7 @@ __device__ __forceinline__ bool ring_stage(int s) { return (s >= 1 && s <= 5) ||
 // of gradients (csi_predict).  MODE 2 / 3: the emulator operator on its own (csi_net_forward / csi_net_vjp, plug
 // point Emulator(backend)): x[n,5] -> y[n,4], and (x, gy) -> gx[n,5]; no priors, likelihood or reduction.
 enum Mode { M_POTENTIAL = 0, M_PREDICT = 1, M_NET_FWD = 2, M_NET_VJP = 3 };
-template <int BC, int MODE>
+template <int BC, int MODE, bool TRACE = false>
 __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_constant__ Launch L) {
   constexpr bool PREDICT = MODE == M_PREDICT, NET = MODE == M_NET_FWD || MODE == M_NET_VJP;
   constexpr bool FWD_ONLY = MODE == M_PREDICT || MODE == M_NET_FWD;
@@ -277,7 +282,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   auto slot_iters = [&](int slot) { return (my_tiles + 1 - slot) / 2; };
 
   // CTA life-cycle marks of the traced CTA: 1 entry, 2 set-up done, 3 all tiles done, 4 reduction done
-  Tracer ctr{(L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ? L.tc.trace + 5 * 1024 : nullptr, 0};
+  Tracer<TRACE> ctr{(L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ? L.tc.trace + 5 * 1024 : nullptr, 0};
   ctr.rec(1);
   // ---- one-time setup ----------------------------------------------------------------------------
   // Warp 11 initialises the barriers and evaluates the hyper-parameter terms (a ~3 k-cycle dependent chain behind
@@ -391,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       while (!__all_sync(full, ptx::mbar_test_wait(bar, parity))) {
       }
     };
-    Tracer tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
+    Tracer<TRACE> tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
     constexpr int kGateStage = FWD_ONLY ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
     uint32_t k = 0, q = 0;            // stage counter of the tile's whole life (region parity); streamed-stage counter
     uint32_t apar0 = 0u, apar1 = 0u;  // parities of the next phases of a_ready[t][0 / 1]
@@ -474,7 +479,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&S.a_ready[t][c]);
     };
-    Tracer tr{nullptr, 0};
+    Tracer<TRACE> tr{nullptr, 0};
     long long *tr_base = nullptr;  // trace of CTA (debug >> 16), starting at this slot's iteration (debug >> 8) & 255
     if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
       tr_base = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
@@ -518,7 +523,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         StarIn in;
         ptx::cp_async_wait_all();
         star_take_z(m, io, col, in);
-        if (tr.p) {  // trace only: stall until the loads have landed so that their latency shows up on its own
+        if (TRACE && tr.p) {  // trace only: stall until the loads have landed so that their latency shows up on its own
           uint32_t x_ = __float_as_uint(in.mloc) ^ __float_as_uint(in.mscale) ^ __float_as_uint(in.mlogz);
 #pragma unroll
           for (int sl = 0; sl < kSlots; ++sl) x_ ^= __float_as_uint(in.zv[sl]);
@@ -528,7 +533,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         star_pre(m, hv, in, st, acc);
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
-        if (tr.p) { if (x[0] + x[1] + x[2] + x[3] + x[4] + st.lp == 1.2345e30f) tr.rec(999); tr.rec(503); }
+        if (TRACE && tr.p) { if (x[0] + x[1] + x[2] + x[3] + x[4] + st.lp == 1.2345e30f) tr.rec(999); tr.rec(503); }
       } else {
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = 0.0f;
@@ -595,7 +600,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             ptx::cp_async_wait_all();
             tr.rec(611);
             star_take_obs(m, io, col, so);
-            if (tr.p) {
+            if (TRACE && tr.p) {
               uint32_t x_ = 0;
 #pragma unroll
               for (int k = 0; k < kMaxMean; ++k) x_ ^= __float_as_uint(so.ob[k]) ^ __float_as_uint(so.dg[k]);
@@ -835,6 +840,7 @@ template <int BC, int MODE>
 static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *smem_out) {
   const int smem = (int)sizeof(tc::Smem) + 1024;
   auto kern = tc::potential_tc_kernel<BC, MODE>;
+  if (BC == 1 && MODE == tc::M_POTENTIAL && L.tc.trace) kern = tc::potential_tc_kernel<BC == 1 ? 1 : 0, tc::M_POTENTIAL, BC == 1 && MODE == tc::M_POTENTIAL>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return -(int)e;
   const long long n_tiles = (L.io.n + tc::kTile - 1) / tc::kTile;
