@@ -126,6 +126,14 @@ __device__ __forceinline__ void split2(float v0, float v1, uint32_t &hi, uint32_
   lo = *reinterpret_cast<uint32_t *>(&ll);
 }
 
+// (a, b) *= s as one packed FP32x2 multiply (SASS FMUL2)
+__device__ __forceinline__ void mul2(float &a, float &b, float s) {
+  asm("{\n\t.reg .b64 v, sc, o;\n\tmov.b64 v, {%0, %1};\n\tmov.b64 sc, {%2, %2};\n\tmul.rn.f32x2 o, v, sc;\n\t"
+      "mov.b64 {%0, %1}, o;\n\t}"
+      : "+f"(a), "+f"(b)
+      : "f"(s));
+}
+
 // byte permute with sign replication (selector nibbles with bit 3 set replicate the msb of the chosen byte)
 template <uint32_t kSel>
 __device__ __forceinline__ uint32_t prmt_sign(uint32_t a) {
@@ -149,8 +157,9 @@ __device__ __forceinline__ void fwd_chunk(const uint32_t (&r)[32], float scale, 
   uint32_t hi[16], lo[16];
 #pragma unroll
   for (int q = 0; q < 16; ++q) {
-    const float v0 = fmaxf(__uint_as_float(r[2 * q]), 0.0f) * scale;
-    const float v1 = fmaxf(__uint_as_float(r[2 * q + 1]), 0.0f) * scale;
+    float v0 = fmaxf(__uint_as_float(r[2 * q]), 0.0f);
+    float v1 = fmaxf(__uint_as_float(r[2 * q + 1]), 0.0f);
+    mul2(v0, v1, scale);
     split2(v0, v1, hi[q], lo[q]);
   }
   ptx::tmem_st16(a_base + 32 * c, hi);       // in place over the D chunk just consumed:
@@ -166,8 +175,12 @@ __device__ __forceinline__ void bwd_chunk(const uint32_t (&r)[32], float f, uint
     const uint32_t ma = prmt_sign<0xAABBu>(w);  // elements 4s (low half), 4s+1 (high half)
     const uint32_t mb = prmt_sign<0x8899u>(w);  // elements 4s+2, 4s+3
     uint32_t h0, l0, h1, l1;
-    split2(__uint_as_float(r[4 * s]) * f, __uint_as_float(r[4 * s + 1]) * f, h0, l0);
-    split2(__uint_as_float(r[4 * s + 2]) * f, __uint_as_float(r[4 * s + 3]) * f, h1, l1);
+    float a0 = __uint_as_float(r[4 * s]), a1 = __uint_as_float(r[4 * s + 1]);
+    float a2 = __uint_as_float(r[4 * s + 2]), a3 = __uint_as_float(r[4 * s + 3]);
+    mul2(a0, a1, f);
+    mul2(a2, a3, f);
+    split2(a0, a1, h0, l0);
+    split2(a2, a3, h1, l1);
     hi[2 * s] = h0 & ~ma; lo[2 * s] = l0 & ~ma;
     hi[2 * s + 1] = h1 & ~mb; lo[2 * s + 1] = l1 & ~mb;
   }
@@ -393,7 +406,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     const uint64_t r7_desc = ptx::make_smem_desc(res + rB7, kLbo, kSbo);
     constexpr uint32_t kSlot16 = 2 * kHalfBytes / 16, kLoOff16 = kHalfBytes / 16, kK128 = kKStepBytes / 16, kK16 = kKStep16 / 16;
     auto wait_bar = [&](uint64_t *bar, uint32_t parity) {
-      while (!__all_sync(full, ptx::mbar_test_wait(bar, parity))) {
+      while (!__all_sync(full, ptx::mbar_try_wait(bar, parity))) {
       }
     };
     Tracer<TRACE> tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
