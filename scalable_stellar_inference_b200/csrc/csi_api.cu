@@ -357,8 +357,16 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
     if (cudaMalloc(&p, sizeof(unsigned int)) != cudaSuccess) rc = fail(CSI_ECUDA, "cudaMalloc counter");
     else { h->owned.push_back(p); h->d_counter = (unsigned int *)p; cudaMemset(p, 0, sizeof(unsigned int)); }
   }
-  if (rc == CSI_OK && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
+  if (rc == CSI_OK && (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
+                       cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess))
     rc = fail(CSI_ECUDA, "cudaStreamCreate");
+  if (rc == CSI_OK) {
+    void *p;
+    if (cudaMalloc(&p, sizeof(unsigned long long)) != cudaSuccess) rc = fail(CSI_ECUDA, "cudaMalloc progress word");
+    else { h->owned.push_back(p); h->d_zflag = (unsigned long long *)p; cudaMemset(p, 0, sizeof(unsigned long long)); }
+    if (rc == CSI_OK && cudaMallocHost(&h->h_zflag_vals, kGateMaxBlocks * sizeof(unsigned long long)) != cudaSuccess)
+      rc = fail(CSI_ECUDA, "cudaMallocHost progress values");
+  }
   if (rc != CSI_OK) { std::string keep = g_err; csi_destroy(h); g_err = keep; return rc; }
   *out = h;
   return CSI_OK;
@@ -383,6 +391,8 @@ extern "C" void csi_destroy(csi_handle *h) {
   free_data(h);
   for (void *p : h->owned) cudaFree(p);
   if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  if (h->h_zflag_vals) cudaFreeHost(h->h_zflag_vals);
   delete h;
 }
 
@@ -504,6 +514,11 @@ static void fill_launch(const csi_handle *h, const float *z, double *out6, float
   L.grad_hyper = (grad && h->n_hyper) ? grad : nullptr;
   L.px = h->px;
   L.sm_count = h->sm_count;
+  if (h->zgate_on) {  // csi_potential_host: hyper-parameters from the caller's buffer, sites from the gated device copy
+    for (int s = 0; s < h->n_sites; ++s) io.z[h->slot_of_site[s]] = h->d_z + h->n_hyper + (long long)s * n;
+    L.z_ready = h->d_zflag;
+    L.z_base = h->zgate_base;
+  }
 }
 
 extern "C" int csi_potential(csi_handle *h, const float *z_dev, double *out_dev, float *grad_dev, void *stream) {
@@ -530,14 +545,62 @@ static void *device_alias_of_host(const void *p) {
   return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
 
+// Gated host-buffer evaluation: the copy engine moves the sites host -> device in star blocks (2-D copies over the
+// [site][star] layout, 55 GB/s) on its own stream and publishes its progress after each block; the kernel, launched
+// at once, stages a tile's sites only when they have been published (Launch::z_ready).  The blocks are whole tile
+// rounds (grid x 128 stars) because the kernel walks the stars round by round; the first one is two rounds (one
+// per tile slot) so that the kernel starts ~20 us after the call, the later ones grow.  The kernel reading the
+// sites over PCIe itself (128-byte reads, issued in bursts by 148 CTAs in step) cost 0.10 ms of a 0.84 ms kernel
+// (profiles/r1_zc_probe.txt); the copy engine stays ahead of the kernel, which consumes 33 GB/s.
+struct GatePlan { int nb; long long bound[kGateMaxBlocks + 1]; };
+
+static void gate_plan(const csi_handle *h, GatePlan &g) {
+  const long long n = h->n_local;
+  const long long n_tiles = (n + 127) / 128;
+  const long long round = 128 * std::min<long long>(n_tiles, h->sm_count);
+  static const int kRounds[] = {2, 4, 8, 12};  // block sizes in rounds, the last one repeats
+  g.nb = 0; g.bound[0] = 0;
+  while (g.bound[g.nb] < n) {
+    long long hi = std::min(n, g.bound[g.nb] + round * kRounds[std::min(g.nb, 3)]);
+    if (g.nb == kGateMaxBlocks - 1) hi = n;
+    g.bound[++g.nb] = hi;
+  }
+}
+
+static int gated_sites_copy(csi_handle *h, const float *z_host, const GatePlan &g, int b0, int b1) {
+  const long long n = h->n_local;
+  for (int b = b0; b < b1; ++b) {
+    const long long lo = g.bound[b], hi = g.bound[b + 1];
+    CK(cudaMemcpy2DAsync(h->d_z + h->n_hyper + lo, (size_t)n * sizeof(float), z_host + h->n_hyper + lo,
+                         (size_t)n * sizeof(float), (size_t)(hi - lo) * sizeof(float), (size_t)h->n_sites,
+                         cudaMemcpyHostToDevice, h->copy_stream));
+    h->h_zflag_vals[b] = h->zgate_base + (unsigned long long)hi;
+    CK(cudaMemcpyAsync(h->d_zflag, h->h_zflag_vals + b, sizeof(unsigned long long), cudaMemcpyHostToDevice,
+                       h->copy_stream));
+  }
+  return CSI_OK;
+}
+
+// CSI_HOST_GATE: 0 (default) = the kernel reads the sites over PCIe itself; 1 = gated copy, every block queued
+// before the launch; 2 = gated copy, the launch follows the first block and the others are queued behind it.
+// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): the gated copy is bit-identical but not faster (the kernel
+// waits ~0.12 ms for the first blocks of the ramp and every progress copy costs the copy engine 10 us), so it stays
+// opt-in.
+static int gate_mode() {  // read per call: a test (or a caller) may switch it between evaluations
+  const char *e = getenv("CSI_HOST_GATE");
+  return e ? atoi(e) : 0;
+}
+
 extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *out_host, float *grad_host) {
   if (!h || !z_host || !out_host || !grad_host) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
   CK(cudaSetDevice(h->device));
   const size_t bytes = (size_t)h->stage_len * sizeof(float);
-  // Page-locked caller buffers are read / written by the kernel itself over PCIe (its input staging runs half a
-  // tile ahead, gradient stores are posted writes): no copy calls, one launch.  Pageable buffers go through the
-  // handle's pinned staging area.
+  // Page-locked caller buffers: one kernel launch, no whole-buffer copy before or after it.  The gradient and the
+  // 6 sums are written by the kernel straight into the caller's memory (posted PCIe writes).  The sites come in
+  // through the gated copy above when the launch is long enough to hide it (tcgen05 engine, >= 8 tile rounds),
+  // else the kernel reads them over PCIe itself (its input staging runs half a tile ahead).  Pageable buffers go
+  // through the handle's pinned staging area.
   const float *z_alias = static_cast<const float *>(device_alias_of_host(z_host));
   float *grad_alias = static_cast<float *>(device_alias_of_host(grad_host));
   const float *z_in = z_alias;
@@ -546,12 +609,33 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
     CK(cudaMemcpyAsync(h->d_z, h->h_z, bytes, cudaMemcpyHostToDevice, h->stream));
     z_in = h->d_z;
   }
+  const bool gated = z_alias && gate_mode() != 0 && h->engine == CSI_ENGINE_TCGEN05 && h->tc.img && !h->tc.debug &&
+                     h->n_local >= 8LL * 128 * h->sm_count;
+  GatePlan plan;
+  int queued = 0;
+  if (gated) {
+    gate_plan(h, plan);
+    h->zgate_base += (unsigned long long)h->n_local + 1;  // the word still holds the last call's base + n < this base
+    queued = gate_mode() == 1 ? plan.nb : 1;
+    int rcg = gated_sites_copy(h, z_host, plan, 0, queued);
+    if (rcg != CSI_OK) { cudaStreamSynchronize(h->copy_stream); return rcg; }
+  }
   double *out_alias = static_cast<double *>(device_alias_of_host(h->h_out));
-  int rc = csi_potential(h, z_in, out_alias ? out_alias : h->d_out, grad_alias ? grad_alias : h->d_grad, h->stream);
-  if (rc != CSI_OK) return rc;
+  static const int exp_bits = getenv("CSI_HOST_GATE_EXP") ? atoi(getenv("CSI_HOST_GATE_EXP")) : 0;  // timing experiments
+  h->zgate_on = gated;
+  if (gated && (exp_bits & 2)) { h->zgate_on = false; z_in = h->d_z; }   // no gate: the kernel reads d_z as it is
+  float *grad_to = (gated && (exp_bits & 1)) ? h->d_grad : (grad_alias ? grad_alias : h->d_grad);
+  int rc = csi_potential(h, z_in, out_alias ? out_alias : h->d_out, grad_to, h->stream);
+  h->zgate_on = false;
+  if (gated) {  // the kernel is waiting for these blocks even when something failed: always queue them
+    int rcg = gated_sites_copy(h, z_host, plan, queued, plan.nb);
+    if (rc == CSI_OK) rc = rcg;
+  }
+  if (rc != CSI_OK) { if (gated) cudaStreamSynchronize(h->copy_stream); cudaStreamSynchronize(h->stream); return rc; }
   if (!grad_alias) CK(cudaMemcpyAsync(h->h_grad, h->d_grad, bytes, cudaMemcpyDeviceToHost, h->stream));
   if (!out_alias) CK(cudaMemcpyAsync(h->h_out, h->d_out, 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
+  if (gated) CK(cudaStreamSynchronize(h->copy_stream));
   if (!grad_alias) memcpy(grad_host, h->h_grad, bytes);
   memcpy(out_host, h->h_out, 6 * sizeof(double));
   return CSI_OK;

@@ -39,6 +39,11 @@ struct Launch {           // everything a potential launch needs
   float *net_y, *net_gx;        // y [n][4], gx [n][5]
   PeerX px;               // fused allreduce over peer memory (world <= 1: off)
   int sm_count;
+  // Gated sites (csi_potential_host): the copy engine fills io.z[] block by block while the kernel runs and
+  // publishes z_base + (stars copied so far) in *z_ready after each block; star i may be staged once
+  // *z_ready - z_base > i.  null = the sites are all there at launch.
+  const unsigned long long *z_ready;
+  unsigned long long z_base;
 };
 
 // returns the number of kernel launches issued (>0) or a negative cudaError
@@ -64,6 +69,8 @@ bool tc_supported(const csi_net &net);
 
 }  // namespace csi
 
+constexpr int kGateMaxBlocks = 64;  // star blocks of the gated host-buffer copy
+
 struct csi_handle {
   int device = 0, sm_count = 0, engine = 0;
   int level = 0, prior = 0;
@@ -88,6 +95,11 @@ struct csi_handle {
   double *h_out = nullptr, *d_out = nullptr;
   long long stage_len = 0;
   cudaStream_t stream = nullptr;
+  // gated host-buffer path: copy stream, progress word (device) and the values the copy engine writes into it
+  cudaStream_t copy_stream = nullptr;
+  unsigned long long *d_zflag = nullptr, *h_zflag_vals = nullptr;
+  unsigned long long zgate_base = 0;
+  bool zgate_on = false;
   csi::PeerX px{};          // csi_set_peer_exchange
   long long last_launches = 0;
   int last_grid = 0, last_smem = 0;

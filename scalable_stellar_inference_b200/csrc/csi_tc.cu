@@ -94,6 +94,7 @@ struct __align__(128) Smem {
   unsigned short grid_lut[4][kLutBins];
   uint64_t w_full[2][2], w_empty[2][2], a_ready[2][2], d_ready[2], start_b;  // a_ready: one barrier per K-half
   uint32_t tmem_base;
+  long long z_seen;              // gated sites: the largest progress value any thread of the CTA has read
   double red[(kThreads / 32) * 6];
   HyperVals hv;
 };
@@ -334,6 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       ptx::mbar_init(&S.d_ready[b], 1);
     }
     ptx::mbar_init(&S.start_b, 1);
+    S.z_seen = 0;
     ptx::fence_barrier_init();
     HyperVals h{};
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
@@ -511,7 +513,21 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 #pragma unroll 4
       for (int j = 0; j < cnt; ++j) ptx::cp_async4(col + l.row[j] * kStageStride, l.src[j] + ii);
     };
-    auto stage_sites = [&](long long ii) { stage(S.sites_list, ii); };
+    // Gated sites (Launch::z_ready): wait until the copy engine has published star ii.  The CTA-wide S.z_seen keeps
+    // the polls to one per published block (stale values only cost another poll; progress is monotone).
+    auto wait_sites = [&](long long ii) {
+      if (NET || !L.z_ready || ii >= n) return;
+      volatile long long *seen = &S.z_seen;
+      if (*seen > ii) return;
+      long long v;
+      int spins = 0;
+      do {
+        v = (long long)(*reinterpret_cast<const volatile unsigned long long *>(L.z_ready) - L.z_base);
+      } while (v <= ii && ++spins < (1 << 20));  // bounded: a lost block shows up as a parity failure, not a hang
+      __threadfence_system();
+      *seen = v;
+    };
+    auto stage_sites = [&](long long ii) { wait_sites(ii); stage(S.sites_list, ii); };
     auto stage_obs = [&](long long ii) { stage(S.obs_list, ii); };
     if (my_iters > 0) stage_sites(((long long)blockIdx.x + t * gridDim.x) * kTile + row);
     if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);

@@ -207,3 +207,33 @@ def test_zero_copy_host_potential_is_bit_identical_to_device_buffers(engine):
         assert u == out[0] and np.array_equal(gh, out[1:6])
         assert np.array_equal(zc.grad_pin.numpy()[5:], np.asarray(grad)[5:])
     assert zc.h2d_bytes == zf.size * 4 and zc.launches == 3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("gate", ["1", "2"])
+def test_gated_host_sites_copy_is_bit_identical_to_device_buffers(gate, monkeypatch):
+    """csi_potential_host on page-locked buffers with CSI_HOST_GATE = 1 / 2 (opt-in; launches of >= 8 tile rounds): the copy engine brings the sites in
+    star blocks while the kernel runs and the kernel stages a tile only once its block has been published
+    (Launch::z_ready).  A different z every call, so a tile staged before its block landed would read the previous
+    call's sites; potential, hyper-gradient and per-star gradient must equal the device-buffer evaluation bit for bit."""
+    from scalable_stellar_inference_b200.parallel import ZeroCopyHostPotential
+    monkeypatch.setenv("CSI_HOST_GATE", gate)
+    name, n = "hier_phot_grid", 230_000
+    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, 1000)
+    rep = n // 1000
+    tile = lambda a: np.tile(np.asarray(a), (rep,) + (1,) * (np.ndim(a) - 1))  # noqa: E731
+    zb = {k: (v if np.ndim(v) == 0 else tile(v)) for k, v in z0.items()}
+    model = PU.product_model(name, n, "tcgen05").condition(tile(obs), tile(diag), M_H_loc=tile(ml), M_H_scale=tile(ms))
+    assert n >= 8 * 128 * model.info()["sm_count"], "the launch must be long enough for the gated path"
+    zf = np.asarray(model.flatten(zb), np.float32)
+    zc = ZeroCopyHostPotential(model)
+    wiggle = np.sin(np.arange(zf.size - 5, dtype=np.float64)).astype(np.float32)
+    for k in range(4):
+        zk = zf.copy()
+        zk[5:] += np.float32(2e-3 * k) * wiggle
+        out, grad = model.potential_and_grad_flat(zk)
+        zc.load(zk)
+        zc.grad_pin.zero_()
+        u, gh, gview = zc.value_and_grad_host()
+        assert np.isfinite(u) and u == out[0] and np.array_equal(gh, out[1:6])
+        assert np.array_equal(zc.grad_pin.numpy()[5:], np.asarray(grad)[5:], equal_nan=True)
