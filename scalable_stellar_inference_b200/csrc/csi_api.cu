@@ -518,6 +518,8 @@ static void fill_launch(const csi_handle *h, const float *z, double *out6, float
     for (int s = 0; s < h->n_sites; ++s) io.z[h->slot_of_site[s]] = h->d_z + h->n_hyper + (long long)s * n;
     L.z_ready = h->d_zflag;
     L.z_base = h->zgate_base;
+    L.z_direct_end = h->zgate_direct_end;
+    L.z_host_delta = h->zgate_host_delta;
   }
 }
 
@@ -550,18 +552,18 @@ static void *device_alias_of_host(const void *p) {
 // at once, stages a tile's sites only when they have been published (Launch::z_ready).  The blocks are whole tile
 // rounds (grid x 128 stars) because the kernel walks the stars round by round; the first one is two rounds (one
 // per tile slot) so that the kernel starts ~20 us after the call, the later ones grow.  The kernel reading the
-// sites over PCIe itself (128-byte reads, issued in bursts by 148 CTAs in step) cost 0.10 ms of a 0.84 ms kernel
-// (profiles/r1_zc_probe.txt); the copy engine stays ahead of the kernel, which consumes 33 GB/s.
+// sites over PCIe itself (128-byte reads, issued in bursts by 148 CTAs in step) costs 0.10 ms on a 0.84 ms kernel
+// (profiles/r1_zc_probe.txt).  Opt-in: see gate_mode() for what was measured.
 struct GatePlan { int nb; long long bound[kGateMaxBlocks + 1]; };
 
-static void gate_plan(const csi_handle *h, GatePlan &g) {
+static void gate_plan(const csi_handle *h, GatePlan &g, int direct_rounds) {
   const long long n = h->n_local;
   const long long n_tiles = (n + 127) / 128;
   const long long round = 128 * std::min<long long>(n_tiles, h->sm_count);
   static const int kRounds[] = {2, 4, 8, 12};  // block sizes in rounds, the last one repeats
-  g.nb = 0; g.bound[0] = 0;
+  g.nb = 0; g.bound[0] = std::min(n, round * direct_rounds);
   while (g.bound[g.nb] < n) {
-    long long hi = std::min(n, g.bound[g.nb] + round * kRounds[std::min(g.nb, 3)]);
+    long long hi = std::min(n, g.bound[g.nb] + round * (direct_rounds ? 12 : kRounds[std::min(g.nb, 3)]));
     if (g.nb == kGateMaxBlocks - 1) hi = n;
     g.bound[++g.nb] = hi;
   }
@@ -582,10 +584,14 @@ static int gated_sites_copy(csi_handle *h, const float *z_host, const GatePlan &
 }
 
 // CSI_HOST_GATE: 0 (default) = the kernel reads the sites over PCIe itself; 1 = gated copy, every block queued
-// before the launch; 2 = gated copy, the launch follows the first block and the others are queued behind it.
-// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): the gated copy is bit-identical but not faster (the kernel
-// waits ~0.12 ms for the first blocks of the ramp and every progress copy costs the copy engine 10 us), so it stays
-// opt-in.
+// before the launch; 2 = gated copy, the launch follows the first block and the others are queued behind it;
+// 3 = hybrid, the kernel is launched first and reads the first CSI_HOST_GATE_DIRECT (14) rounds from the caller's
+// buffer itself while the copy engine brings the rest in gated blocks of 12 rounds.
+// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): all three are bit-identical to mode 0 and all three are
+// slower (620-940 / 690-840 evals/s against 905-967), although the same block copies alone run at 46 GB/s
+// (profiles/r1_ce_probe.txt): copy-engine transfers that overlap this persistent kernel and its posted gradient
+// writes lose more than the kernel's own 128-byte PCIe reads cost (+0.10 ms, profiles/r1_zc_probe.txt).  Opt-in,
+// kept for the record and for PCIe topologies where zero-copy reads are slower.
 static int gate_mode() {  // read per call: a test (or a caller) may switch it between evaluations
   const char *e = getenv("CSI_HOST_GATE");
   return e ? atoi(e) : 0;
@@ -597,10 +603,10 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
   CK(cudaSetDevice(h->device));
   const size_t bytes = (size_t)h->stage_len * sizeof(float);
   // Page-locked caller buffers: one kernel launch, no whole-buffer copy before or after it.  The gradient and the
-  // 6 sums are written by the kernel straight into the caller's memory (posted PCIe writes).  The sites come in
-  // through the gated copy above when the launch is long enough to hide it (tcgen05 engine, >= 8 tile rounds),
-  // else the kernel reads them over PCIe itself (its input staging runs half a tile ahead).  Pageable buffers go
-  // through the handle's pinned staging area.
+  // 6 sums are written by the kernel straight into the caller's memory (posted PCIe writes) and it reads the sites
+  // over PCIe itself (its input staging runs half a tile ahead); with CSI_HOST_GATE != 0 (tcgen05 engine, >= 8 tile
+  // rounds) the sites come in through the gated copy above instead.  Pageable buffers go through the handle's
+  // pinned staging area.
   const float *z_alias = static_cast<const float *>(device_alias_of_host(z_host));
   float *grad_alias = static_cast<float *>(device_alias_of_host(grad_host));
   const float *z_in = z_alias;
@@ -614,9 +620,14 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
   GatePlan plan;
   int queued = 0;
   if (gated) {
-    gate_plan(h, plan);
+    // mode 3: the kernel reads the first rounds from the caller's buffer itself and is launched first
+    const char *dr = getenv("CSI_HOST_GATE_DIRECT");
+    const int direct_rounds = gate_mode() == 3 ? (dr ? std::max(1, atoi(dr)) : 14) : 0;
+    gate_plan(h, plan, direct_rounds);
+    h->zgate_direct_end = plan.bound[0];
+    h->zgate_host_delta = ((long long)(intptr_t)z_alias - (long long)(intptr_t)h->d_z) / (long long)sizeof(float);
     h->zgate_base += (unsigned long long)h->n_local + 1;  // the word still holds the last call's base + n < this base
-    queued = gate_mode() == 1 ? plan.nb : 1;
+    queued = gate_mode() == 1 ? plan.nb : gate_mode() == 3 ? 0 : 1;
     int rcg = gated_sites_copy(h, z_host, plan, 0, queued);
     if (rcg != CSI_OK) { cudaStreamSynchronize(h->copy_stream); return rcg; }
   }

@@ -44,6 +44,9 @@ struct Launch {           // everything a potential launch needs
   // *z_ready - z_base > i.  null = the sites are all there at launch.
   const unsigned long long *z_ready;
   unsigned long long z_base;
+  // hybrid: stars below z_direct_end are read from the caller's page-locked buffer itself (= io.z[] + z_host_delta
+  // floats, no gate), so the kernel starts at once while the copy engine works on the blocks behind them
+  long long z_direct_end, z_host_delta;
 };
 
 // returns the number of kernel launches issued (>0) or a negative cudaError
@@ -100,6 +103,7 @@ struct csi_handle {
   unsigned long long *d_zflag = nullptr, *h_zflag_vals = nullptr;
   unsigned long long zgate_base = 0;
   bool zgate_on = false;
+  long long zgate_direct_end = 0, zgate_host_delta = 0;
   csi::PeerX px{};          // csi_set_peer_exchange
   long long last_launches = 0;
   int last_grid = 0, last_smem = 0;

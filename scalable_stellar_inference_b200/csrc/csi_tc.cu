@@ -527,7 +527,17 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       __threadfence_system();
       *seen = v;
     };
-    auto stage_sites = [&](long long ii) { wait_sites(ii); stage(S.sites_list, ii); };
+    auto stage_sites = [&](long long ii) {
+      if (!L.z_ready) { stage(S.sites_list, ii); return; }
+      if (NET || ii >= n) return;
+      long long delta = 0;  // sites below z_direct_end come from the caller's buffer, the others from the gated copy
+      if (ii < L.z_direct_end) delta = L.z_host_delta; else wait_sites(ii);
+      const StageList &l = S.sites_list;
+      const int cnt = l.n;
+#pragma unroll 4
+      for (int j = 0; j < cnt; ++j)
+        ptx::cp_async4(col + l.row[j] * kStageStride, l.src[j] + ii + (l.row[j] < kSlots ? delta : 0));
+    };
     auto stage_obs = [&](long long ii) { stage(S.obs_list, ii); };
     if (my_iters > 0) stage_sites(((long long)blockIdx.x + t * gridDim.x) * kTile + row);
     if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);

@@ -210,7 +210,7 @@ def test_zero_copy_host_potential_is_bit_identical_to_device_buffers(engine):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("gate", ["1", "2"])
+@pytest.mark.parametrize("gate", ["1", "2", "3"])
 def test_gated_host_sites_copy_is_bit_identical_to_device_buffers(gate, monkeypatch):
     """csi_potential_host on page-locked buffers with CSI_HOST_GATE = 1 / 2 (opt-in; launches of >= 8 tile rounds): the copy engine brings the sites in
     star blocks while the kernel runs and the kernel stages a tile only once its block has been published
@@ -218,6 +218,7 @@ def test_gated_host_sites_copy_is_bit_identical_to_device_buffers(gate, monkeypa
     call's sites; potential, hyper-gradient and per-star gradient must equal the device-buffer evaluation bit for bit."""
     from scalable_stellar_inference_b200.parallel import ZeroCopyHostPotential
     monkeypatch.setenv("CSI_HOST_GATE", gate)
+    monkeypatch.setenv("CSI_HOST_GATE_DIRECT", "3")  # mode 3: the first 3 rounds straight from the caller's buffer
     name, n = "hier_phot_grid", 230_000
     spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, 1000)
     rep = n // 1000
