@@ -586,9 +586,10 @@ static int gated_sites_copy(csi_handle *h, const float *z_host, const GatePlan &
 // CSI_HOST_GATE: 0 (default) = the kernel reads the sites over PCIe itself; 1 = gated copy, every block queued
 // before the launch; 2 = gated copy, the launch follows the first block and the others are queued behind it;
 // 3 = hybrid, the kernel is launched first and reads the first CSI_HOST_GATE_DIRECT (14) rounds from the caller's
-// buffer itself while the copy engine brings the rest in gated blocks of 12 rounds.
-// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): all three are bit-identical to mode 0 and all three are
-// slower (620-940 / 690-840 evals/s against 905-967), although the same block copies alone run at 46 GB/s
+// buffer itself while the copy engine brings the rest in gated blocks of 12 rounds; 4 = as 3 with every block
+// queued before the launch.
+// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): all are bit-identical to mode 0 and all are slower
+// (620-940 / 690-840 / 630-700 evals/s against 905-967), although the same block copies alone run at 46 GB/s
 // (profiles/r1_ce_probe.txt): copy-engine transfers that overlap this persistent kernel and its posted gradient
 // writes lose more than the kernel's own 128-byte PCIe reads cost (+0.10 ms, profiles/r1_zc_probe.txt).  Opt-in,
 // kept for the record and for PCIe topologies where zero-copy reads are slower.
@@ -622,12 +623,12 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
   if (gated) {
     // mode 3: the kernel reads the first rounds from the caller's buffer itself and is launched first
     const char *dr = getenv("CSI_HOST_GATE_DIRECT");
-    const int direct_rounds = gate_mode() == 3 ? (dr ? std::max(1, atoi(dr)) : 14) : 0;
+    const int direct_rounds = gate_mode() >= 3 ? (dr ? std::max(1, atoi(dr)) : 14) : 0;  // 4: as 3, copies queued first
     gate_plan(h, plan, direct_rounds);
     h->zgate_direct_end = plan.bound[0];
     h->zgate_host_delta = ((long long)(intptr_t)z_alias - (long long)(intptr_t)h->d_z) / (long long)sizeof(float);
     h->zgate_base += (unsigned long long)h->n_local + 1;  // the word still holds the last call's base + n < this base
-    queued = gate_mode() == 1 ? plan.nb : gate_mode() == 3 ? 0 : 1;
+    queued = (gate_mode() == 1 || gate_mode() == 4) ? plan.nb : gate_mode() == 3 ? 0 : 1;
     int rcg = gated_sites_copy(h, z_host, plan, 0, queued);
     if (rcg != CSI_OK) { cudaStreamSynchronize(h->copy_stream); return rcg; }
   }

@@ -355,6 +355,10 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
+  if (L.tc.debug & 32) {  // timing experiment: CTAs start in four phases 8 us apart (de-phased PCIe staging bursts)
+    const long long t0 = clock64();
+    while (clock64() - t0 < (long long)(blockIdx.x & 3) * 14000) {}
+  }
   const uint32_t tmem = S.tmem_base;
   const HyperVals hv = S.hv;
   HyperAcc acc{};

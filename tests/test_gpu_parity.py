@@ -210,7 +210,7 @@ def test_zero_copy_host_potential_is_bit_identical_to_device_buffers(engine):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("gate", ["1", "2", "3"])
+@pytest.mark.parametrize("gate", ["1", "2", "3", "4"])
 def test_gated_host_sites_copy_is_bit_identical_to_device_buffers(gate, monkeypatch):
     """csi_potential_host on page-locked buffers with CSI_HOST_GATE = 1 / 2 (opt-in; launches of >= 8 tile rounds): the copy engine brings the sites in
     star blocks while the kernel runs and the kernel stages a tile only once its block has been published
