@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define CSI_VERSION 100
+#define CSI_VERSION 200
 
 #define CSI_OK 0
 #define CSI_EINVAL (-1)    /* bad argument / unsupported configuration */
@@ -118,12 +118,16 @@ void csi_destroy(csi_handle *h);
 int csi_set_shard(csi_handle *h, int32_t rank, int32_t world);
 
 /* Fused allreduce of `out` (no reference equivalent: the reference never shards the star axis).  peer_bufs[r] is
- * a device pointer, valid in THIS process, to rank r's exchange buffer of 2 * world * 8 doubles, zero-initialised
- * and writable by all ranks over NVLink peer memory (CUDA IPC / symmetric memory; peer_bufs[rank] is the caller's
- * own).  Afterwards the finalising block of every csi_potential stores its 6 sums into all ranks' buffers and adds
- * the world's contributions in rank order, so `out` (and the hyper slots of grad) hold the GLOBAL sums and no
- * separate collective call is needed.  All ranks must call csi_potential the same number of times.  world <= 1
- * or peer_bufs == NULL switches it off. */
+ * a device pointer, valid in THIS process, to rank r's exchange buffer of CSI_PEER_BUF_DOUBLES(world) doubles,
+ * zero-initialised and writable by all ranks over NVLink peer memory (CUDA IPC / symmetric memory; peer_bufs[rank]
+ * is the caller's own).  Afterwards the finalising block of every csi_potential stores its 6 sums into all ranks'
+ * buffers and adds the world's contributions in rank order, so `out` (and the hyper slots of grad) hold the GLOBAL
+ * sums and no separate collective call is needed; the device-side sampler (csi_nuts_*) sends its inner products
+ * through the same buffers.  The exchange epoch lives in device memory and is advanced by the kernels themselves,
+ * so launches may be captured into CUDA graphs and replayed.  All ranks must issue the same sequence of calls.
+ * world <= 1 or peer_bufs == NULL switches it off. */
+#define CSI_PEER_SLOT_DOUBLES 32
+#define CSI_PEER_BUF_DOUBLES(world) (2 * (world) * CSI_PEER_SLOT_DOUBLES)
 int csi_set_peer_exchange(csi_handle *h, int32_t world, int32_t rank, void *const *peer_bufs);
 
 /* Observations of the local stars.  Replaces the `obs=` / `diag=` arguments of model.__call__
@@ -132,6 +136,10 @@ int csi_set_peer_exchange(csi_handle *h, int32_t world, int32_t rank, void *cons
  * or NULL (= the constants of cfg.m_h). */
 int csi_set_data(csi_handle *h, int64_t n_local, const double *obs, const double *diag,
                  const double *mh_loc, const double *mh_scale);
+
+/* At most max_ctas thread blocks per csi_potential launch (0 = one per SM, the default): lets several chains, each
+ * with its own handle and stream, evaluate side by side on one GPU. */
+int csi_set_grid_limit(csi_handle *h, int32_t max_ctas);
 
 /* Layout of the unconstrained vector: [hyper sites (n_hyper) | star site 0 (n_local) | star site 1 ...],
  * sites in the reference's trace order (numpyro_models.py:279-288 then :148-196 / :301-331).
@@ -143,7 +151,10 @@ int csi_layout(const csi_handle *h, int32_t *n_hyper, int32_t *n_star_sites, con
  *   z_dev    : float[n_hyper + n_sites*n_local]
  *   out_dev  : double[1 + CSI_MAX_HYPER] = [U_local, dU/dhyper (local partial sums)]  -- allreduce this
  *   grad_dev : float[n_hyper + n_sites*n_local]; the hyper slots receive the LOCAL partials in fp32
- * Stream-ordered, no host synchronisation, no allocation. `stream` is a cudaStream_t (NULL = legacy default). */
+ * Stream-ordered, no host synchronisation, no allocation. `stream` is a cudaStream_t (NULL = legacy default).
+ * The handle's device must be the caller's current device (CSI_ESTATE otherwise; the call never switches it).
+ * Domain: the tcgen05 engine carries activations as fp16 pairs scaled by 2^9, so hidden activations must stay
+ * below ~127 (the shipped emulator reaches ~6 inside the prior box); beyond that the result is NaN -- a value. */
 int csi_potential(csi_handle *h, const float *z_dev, double *out_dev, float *grad_dev, void *stream);
 
 /* Same through HOST buffers, synchronous.  Page-locked (cudaHostAlloc / cudaHostRegister) z_host / grad_host are
@@ -200,6 +211,45 @@ int csi_leapfrog_post(csi_handle *h, const float *r_half, const float *grad, con
  * same two over the hyper entries; turning iff dots4[0]+dots4[2] <= 0 or dots4[1]+dots4[3] <= 0. */
 int csi_uturn(csi_handle *h, const float *r_left, const float *r_right, const float *r_sum, const float *inv_mass,
               double *dots4, void *stream);
+
+/* ---- the sampler itself: No-U-Turn transitions with the tree logic on the device ----------------------------------
+ * Replaces numpyro.infer.NUTS / MCMC as driven by scripts/model_star.py:132-155 (multinomial NUTS, iterative
+ * sub-tree building with checkpointed U-turn tests, biased progressive sampling; numpyro/infer/hmc_util.py).
+ * z_state / g_state / inv_mass are device vectors float[n_hyper + n_sites*n_local] owned by the CALLER:
+ * z_state / g_state hold the current position and dU/dz and are updated in place by every transition; inv_mass
+ * (diagonal inverse mass matrix) may be rewritten between transitions.  Everything else lives in the object.
+ * One leapfrog = 3 launches (half step, csi_potential, half step + tree bookkeeping), a doubling = one CUDA graph;
+ * the host synchronises once per doubling.  Random decisions come from a counter-based hash of (seed, draw, ...):
+ * runs are bit-reproducible, and for sharded runs (csi_set_shard + csi_set_peer_exchange; star_offset = global
+ * index of the first local star, n_total = all stars) every rank takes the same decisions. */
+typedef struct csi_nuts csi_nuts;
+typedef struct csi_nuts_stats {
+  double potential;    /* U at the new state */
+  double accept_prob;  /* mean acceptance probability over the leaves built (dual-averaging statistic) */
+  double energy0;      /* H at the start of the transition */
+  int64_t num_leapfrog;
+  int64_t launches;    /* kernel launches queued (graph nodes counted) */
+  int32_t depth, diverging, turning, host_syncs;
+} csi_nuts_stats;
+int csi_nuts_create(csi_handle *h, float *z_state_dev, float *g_state_dev, const float *inv_mass_dev,
+                    int32_t max_tree_depth, double max_delta_energy, uint64_t seed, int64_t star_offset,
+                    int64_t n_total, csi_nuts **out);
+void csi_nuts_destroy(csi_nuts *s);
+/* Evaluates U and dU/dz at z_state (into g_state); call once before the first transition and whenever z_state has
+ * been overwritten by the caller. */
+int csi_nuts_init_state(csi_nuts *s, double *u_out);
+/* One NUTS transition with step size `step_size`; `draw` numbers the transition (random stream). */
+int csi_nuts_transition(csi_nuts *s, double step_size, uint64_t draw, csi_nuts_stats *stats);
+/* Energy change of ONE leapfrog with a fresh momentum from the current state (left untouched): the probe of
+ * find_heuristic_step_size (scripts/model_star.py:20). */
+int csi_nuts_probe_step(csi_nuts *s, double step_size, uint64_t draw, double *delta_energy);
+/* Test access: run only the momentum draw of a transition; copy an internal vector to the host
+ * (0 z_left, 1 r_left, 2 g_left, 3 z_right, 4 r_right, 5 g_right, 6 r_sum). */
+int csi_nuts_begin_only(csi_nuts *s, double step_size, uint64_t draw);
+int csi_nuts_peek(csi_nuts *s, int32_t which, float *out_host);
+/* The counter-based hash behind every random decision (kind 1 momentum, 2 direction, 3 leaf accept, 4 merge);
+ * needs no device.  uniform = (hash >> 11) * 2^-53. */
+uint64_t csi_nuts_hash(uint64_t seed, uint64_t draw, uint64_t kind, uint64_t idx);
 
 /* Times `iters` back-to-back csi_potential calls on the handle's own stream with CUDA events recorded on
  * that stream; returns the mean milliseconds per call.  Used by bench.py for the roofline numbers. */

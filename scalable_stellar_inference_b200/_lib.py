@@ -59,6 +59,15 @@ class Config(C.Structure):
                 ("device", C.c_int32), ("engine", C.c_int32)]
 
 
+class NutsStats(C.Structure):
+    _fields_ = [("potential", C.c_double), ("accept_prob", C.c_double), ("energy0", C.c_double),
+                ("num_leapfrog", C.c_int64), ("launches", C.c_int64), ("depth", C.c_int32), ("diverging", C.c_int32),
+                ("turning", C.c_int32), ("host_syncs", C.c_int32)]
+
+
+PEER_SLOT_DOUBLES = 32
+
+
 _PROTOS = {
     "csi_last_error": (C.c_char_p, []),
     "csi_version": (C.c_int, []),
@@ -67,12 +76,22 @@ _PROTOS = {
     "csi_set_shard": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32]),
     "csi_set_peer_exchange": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "csi_set_data": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "csi_set_grid_limit": (C.c_int, [C.c_void_p, C.c_int32]),
     "csi_layout": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_char_p)]),
     "csi_potential": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "csi_potential_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "csi_leapfrog_pre": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
     "csi_leapfrog_post": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
     "csi_uturn": (C.c_int, [C.c_void_p] * 7),
+    "csi_nuts_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_uint64,
+                                  C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]),
+    "csi_nuts_destroy": (None, [C.c_void_p]),
+    "csi_nuts_init_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "csi_nuts_transition": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.POINTER(NutsStats)]),
+    "csi_nuts_probe_step": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64, C.POINTER(C.c_double)]),
+    "csi_nuts_begin_only": (C.c_int, [C.c_void_p, C.c_double, C.c_uint64]),
+    "csi_nuts_peek": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),
+    "csi_nuts_hash": (C.c_uint64, [C.c_uint64] * 4),
     "csi_net_forward": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "csi_net_vjp": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "csi_grid_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

@@ -357,15 +357,12 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
     if (cudaMalloc(&p, sizeof(unsigned int)) != cudaSuccess) rc = fail(CSI_ECUDA, "cudaMalloc counter");
     else { h->owned.push_back(p); h->d_counter = (unsigned int *)p; cudaMemset(p, 0, sizeof(unsigned int)); }
   }
-  if (rc == CSI_OK && (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess ||
-                       cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess))
+  if (rc == CSI_OK && cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess)
     rc = fail(CSI_ECUDA, "cudaStreamCreate");
   if (rc == CSI_OK) {
     void *p;
-    if (cudaMalloc(&p, sizeof(unsigned long long)) != cudaSuccess) rc = fail(CSI_ECUDA, "cudaMalloc progress word");
-    else { h->owned.push_back(p); h->d_zflag = (unsigned long long *)p; cudaMemset(p, 0, sizeof(unsigned long long)); }
-    if (rc == CSI_OK && cudaMallocHost(&h->h_zflag_vals, kGateMaxBlocks * sizeof(unsigned long long)) != cudaSuccess)
-      rc = fail(CSI_ECUDA, "cudaMallocHost progress values");
+    if (cudaMalloc(&p, sizeof(unsigned long long)) != cudaSuccess) rc = fail(CSI_ECUDA, "cudaMalloc exchange epoch");
+    else { h->owned.push_back(p); h->d_epoch = (unsigned long long *)p; cudaMemset(p, 0, sizeof(unsigned long long)); }
   }
   if (rc != CSI_OK) { std::string keep = g_err; csi_destroy(h); g_err = keep; return rc; }
   *out = h;
@@ -391,8 +388,6 @@ extern "C" void csi_destroy(csi_handle *h) {
   free_data(h);
   for (void *p : h->owned) cudaFree(p);
   if (h->stream) cudaStreamDestroy(h->stream);
-  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
-  if (h->h_zflag_vals) cudaFreeHost(h->h_zflag_vals);
   delete h;
 }
 
@@ -412,8 +407,19 @@ extern "C" int csi_set_peer_exchange(csi_handle *h, int32_t world, int32_t rank,
     if (!peer_bufs[r]) return fail(CSI_EINVAL, "peer exchange: null buffer");
     px.bufs[r] = static_cast<double *>(peer_bufs[r]);
   }
-  px.world = world; px.rank = rank; px.epoch = 0;
+  px.world = world; px.rank = rank; px.epoch = h->d_epoch;
+  // a missing peer turns into NaN after this long (default 5 s; CSI_PEER_TIMEOUT_MS for tests)
+  const char *tmo = getenv("CSI_PEER_TIMEOUT_MS");
+  px.timeout_ns = (unsigned long long)(tmo && atof(tmo) > 0 ? atof(tmo) : 5000.0) * 1000000ull;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemset(h->d_epoch, 0, sizeof(unsigned long long)));  // every rank restarts the count with its (zeroed) buffer
   h->px = px;
+  return CSI_OK;
+}
+
+extern "C" int csi_set_grid_limit(csi_handle *h, int32_t max_ctas) {
+  if (!h || max_ctas < 0) return fail(CSI_EINVAL, "bad grid limit");
+  h->grid_limit = max_ctas;
   return CSI_OK;
 }
 
@@ -514,20 +520,25 @@ static void fill_launch(const csi_handle *h, const float *z, double *out6, float
   L.grad_hyper = (grad && h->n_hyper) ? grad : nullptr;
   L.px = h->px;
   L.sm_count = h->sm_count;
-  if (h->zgate_on) {  // csi_potential_host: hyper-parameters from the caller's buffer, sites from the gated device copy
-    for (int s = 0; s < h->n_sites; ++s) io.z[h->slot_of_site[s]] = h->d_z + h->n_hyper + (long long)s * n;
-    L.z_ready = h->d_zflag;
-    L.z_base = h->zgate_base;
-    L.z_direct_end = h->zgate_direct_end;
-    L.z_host_delta = h->zgate_host_delta;
-  }
+  L.stop = h->stop_flag;
+  L.grid_limit = h->grid_limit;
+}
+
+// The stream-ordered entry points never change the caller's current device; they refuse to launch on another one
+// (the handle's pointers belong to h->device, and the null stream is the current device's).
+static int check_device(const csi_handle *h) {
+  int cur = -1;
+  if (cudaGetDevice(&cur) != cudaSuccess || cur != h->device)
+    return fail(CSI_ESTATE, "current CUDA device " + std::to_string(cur) + " is not the handle's device " +
+                                std::to_string(h->device) + ": call cudaSetDevice first");
+  return CSI_OK;
 }
 
 extern "C" int csi_potential(csi_handle *h, const float *z_dev, double *out_dev, float *grad_dev, void *stream) {
   if (!h || !z_dev || !out_dev || !grad_dev) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
+  if (int rcd = check_device(h)) return rcd;
   Launch L;
-  if (h->px.world > 1) ++h->px.epoch;  // one collective epoch per evaluation, the same count on every rank
   fill_launch(h, z_dev, out_dev, grad_dev, L);
   cudaStream_t st = (cudaStream_t)stream;
   int rc = h->engine == CSI_ENGINE_TCGEN05 ? launch_potential_tc(L, st, &h->last_grid, &h->last_smem)
@@ -547,57 +558,6 @@ static void *device_alias_of_host(const void *p) {
   return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
 }
 
-// Gated host-buffer evaluation: the copy engine moves the sites host -> device in star blocks (2-D copies over the
-// [site][star] layout, 55 GB/s) on its own stream and publishes its progress after each block; the kernel, launched
-// at once, stages a tile's sites only when they have been published (Launch::z_ready).  The blocks are whole tile
-// rounds (grid x 128 stars) because the kernel walks the stars round by round; the first one is two rounds (one
-// per tile slot) so that the kernel starts ~20 us after the call, the later ones grow.  The kernel reading the
-// sites over PCIe itself (128-byte reads, issued in bursts by 148 CTAs in step) costs 0.10 ms on a 0.84 ms kernel
-// (profiles/r1_zc_probe.txt).  Opt-in: see gate_mode() for what was measured.
-struct GatePlan { int nb; long long bound[kGateMaxBlocks + 1]; };
-
-static void gate_plan(const csi_handle *h, GatePlan &g, int direct_rounds) {
-  const long long n = h->n_local;
-  const long long n_tiles = (n + 127) / 128;
-  const long long round = 128 * std::min<long long>(n_tiles, h->sm_count);
-  static const int kRounds[] = {2, 4, 8, 12};  // block sizes in rounds, the last one repeats
-  g.nb = 0; g.bound[0] = std::min(n, round * direct_rounds);
-  while (g.bound[g.nb] < n) {
-    long long hi = std::min(n, g.bound[g.nb] + round * (direct_rounds ? 12 : kRounds[std::min(g.nb, 3)]));
-    if (g.nb == kGateMaxBlocks - 1) hi = n;
-    g.bound[++g.nb] = hi;
-  }
-}
-
-static int gated_sites_copy(csi_handle *h, const float *z_host, const GatePlan &g, int b0, int b1) {
-  const long long n = h->n_local;
-  for (int b = b0; b < b1; ++b) {
-    const long long lo = g.bound[b], hi = g.bound[b + 1];
-    CK(cudaMemcpy2DAsync(h->d_z + h->n_hyper + lo, (size_t)n * sizeof(float), z_host + h->n_hyper + lo,
-                         (size_t)n * sizeof(float), (size_t)(hi - lo) * sizeof(float), (size_t)h->n_sites,
-                         cudaMemcpyHostToDevice, h->copy_stream));
-    h->h_zflag_vals[b] = h->zgate_base + (unsigned long long)hi;
-    CK(cudaMemcpyAsync(h->d_zflag, h->h_zflag_vals + b, sizeof(unsigned long long), cudaMemcpyHostToDevice,
-                       h->copy_stream));
-  }
-  return CSI_OK;
-}
-
-// CSI_HOST_GATE: 0 (default) = the kernel reads the sites over PCIe itself; 1 = gated copy, every block queued
-// before the launch; 2 = gated copy, the launch follows the first block and the others are queued behind it;
-// 3 = hybrid, the kernel is launched first and reads the first CSI_HOST_GATE_DIRECT (14) rounds from the caller's
-// buffer itself while the copy engine brings the rest in gated blocks of 12 rounds; 4 = as 3 with every block
-// queued before the launch.
-// Measured at 1 M stars (profiles/r1_host_gate_ab.txt): all are bit-identical to mode 0 and all are slower
-// (620-940 / 690-840 / 630-700 evals/s against 905-967), although the same block copies alone run at 46 GB/s
-// (profiles/r1_ce_probe.txt): copy-engine transfers that overlap this persistent kernel and its posted gradient
-// writes lose more than the kernel's own 128-byte PCIe reads cost (+0.10 ms, profiles/r1_zc_probe.txt).  Opt-in,
-// kept for the record and for PCIe topologies where zero-copy reads are slower.
-static int gate_mode() {  // read per call: a test (or a caller) may switch it between evaluations
-  const char *e = getenv("CSI_HOST_GATE");
-  return e ? atoi(e) : 0;
-}
-
 extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *out_host, float *grad_host) {
   if (!h || !z_host || !out_host || !grad_host) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
@@ -605,9 +565,9 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
   const size_t bytes = (size_t)h->stage_len * sizeof(float);
   // Page-locked caller buffers: one kernel launch, no whole-buffer copy before or after it.  The gradient and the
   // 6 sums are written by the kernel straight into the caller's memory (posted PCIe writes) and it reads the sites
-  // over PCIe itself (its input staging runs half a tile ahead); with CSI_HOST_GATE != 0 (tcgen05 engine, >= 8 tile
-  // rounds) the sites come in through the gated copy above instead.  Pageable buffers go through the handle's
-  // pinned staging area.
+  // over PCIe itself (its input staging runs half a tile ahead).  Pageable buffers go through the handle's pinned
+  // staging area.  (Copy-engine staging of the sites behind a progress word was measured slower and removed:
+  // profiles/r1_host_gate_ab.txt)
   const float *z_alias = static_cast<const float *>(device_alias_of_host(z_host));
   float *grad_alias = static_cast<float *>(device_alias_of_host(grad_host));
   const float *z_in = z_alias;
@@ -616,38 +576,12 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
     CK(cudaMemcpyAsync(h->d_z, h->h_z, bytes, cudaMemcpyHostToDevice, h->stream));
     z_in = h->d_z;
   }
-  const bool gated = z_alias && gate_mode() != 0 && h->engine == CSI_ENGINE_TCGEN05 && h->tc.img && !h->tc.debug &&
-                     h->n_local >= 8LL * 128 * h->sm_count;
-  GatePlan plan;
-  int queued = 0;
-  if (gated) {
-    // mode 3: the kernel reads the first rounds from the caller's buffer itself and is launched first
-    const char *dr = getenv("CSI_HOST_GATE_DIRECT");
-    const int direct_rounds = gate_mode() >= 3 ? (dr ? std::max(1, atoi(dr)) : 14) : 0;  // 4: as 3, copies queued first
-    gate_plan(h, plan, direct_rounds);
-    h->zgate_direct_end = plan.bound[0];
-    h->zgate_host_delta = ((long long)(intptr_t)z_alias - (long long)(intptr_t)h->d_z) / (long long)sizeof(float);
-    h->zgate_base += (unsigned long long)h->n_local + 1;  // the word still holds the last call's base + n < this base
-    queued = (gate_mode() == 1 || gate_mode() == 4) ? plan.nb : gate_mode() == 3 ? 0 : 1;
-    int rcg = gated_sites_copy(h, z_host, plan, 0, queued);
-    if (rcg != CSI_OK) { cudaStreamSynchronize(h->copy_stream); return rcg; }
-  }
   double *out_alias = static_cast<double *>(device_alias_of_host(h->h_out));
-  static const int exp_bits = getenv("CSI_HOST_GATE_EXP") ? atoi(getenv("CSI_HOST_GATE_EXP")) : 0;  // timing experiments
-  h->zgate_on = gated;
-  if (gated && (exp_bits & 2)) { h->zgate_on = false; z_in = h->d_z; }   // no gate: the kernel reads d_z as it is
-  float *grad_to = (gated && (exp_bits & 1)) ? h->d_grad : (grad_alias ? grad_alias : h->d_grad);
-  int rc = csi_potential(h, z_in, out_alias ? out_alias : h->d_out, grad_to, h->stream);
-  h->zgate_on = false;
-  if (gated) {  // the kernel is waiting for these blocks even when something failed: always queue them
-    int rcg = gated_sites_copy(h, z_host, plan, queued, plan.nb);
-    if (rc == CSI_OK) rc = rcg;
-  }
-  if (rc != CSI_OK) { if (gated) cudaStreamSynchronize(h->copy_stream); cudaStreamSynchronize(h->stream); return rc; }
+  int rc = csi_potential(h, z_in, out_alias ? out_alias : h->d_out, grad_alias ? grad_alias : h->d_grad, h->stream);
+  if (rc != CSI_OK) { cudaStreamSynchronize(h->stream); return rc; }
   if (!grad_alias) CK(cudaMemcpyAsync(h->h_grad, h->d_grad, bytes, cudaMemcpyDeviceToHost, h->stream));
   if (!out_alias) CK(cudaMemcpyAsync(h->h_out, h->d_out, 6 * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  if (gated) CK(cudaStreamSynchronize(h->copy_stream));
   if (!grad_alias) memcpy(grad_host, h->h_grad, bytes);
   memcpy(out_host, h->h_out, 6 * sizeof(double));
   return CSI_OK;
@@ -656,8 +590,10 @@ extern "C" int csi_potential_host(csi_handle *h, const float *z_host, double *ou
 extern "C" int csi_predict(csi_handle *h, const float *z_dev, float *mean_dev, float *params_dev, void *stream) {
   if (!h || !z_dev) return fail(CSI_EINVAL, "null argument");
   if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
+  if (int rcd = check_device(h)) return rcd;
   Launch L;
   fill_launch(h, z_dev, nullptr, nullptr, L);
+  L.stop = nullptr;
   L.mean_out = mean_dev; L.params_out = params_dev;
   int rc = h->engine == CSI_ENGINE_TCGEN05 ? launch_predict_tc(L, (cudaStream_t)stream)
                                            : launch_predict_ffma(L, (cudaStream_t)stream);

@@ -37,6 +37,7 @@ template <int BC, bool PREDICT>
 __global__ void __launch_bounds__(kRows) potential_ffma_kernel(const __grid_constant__ Launch L) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FfmaSmem &S = *reinterpret_cast<FfmaSmem *>(smem_raw);
+  if (L.stop != nullptr && *reinterpret_cast<const volatile int *>(L.stop) != 0) return;  // skipped leapfrog (csi_nuts.cuh)
   const DevModel &m = L.model;
   const StarIO &io = L.io;
   load_hyper(m, io, &S.hv);

@@ -18,8 +18,8 @@ struct TcWeights {
   const uint8_t *resident; // images of the four narrow stages (layer 0, 6, 6^T, 0^T), kept in shared memory
   const float *small;      // packed fp32 scalings / gains
   int n_steps;
-  long long *trace;        // CSI_TC_DEBUG & 8: clock64 trace of CTA 0 (csi_tc_trace)
-  int debug;               // CSI_TC_DEBUG experiments (timing only; results are wrong when non-zero)
+  long long *trace;        // CSI_TC_DEBUG=8: clock64 trace of one CTA (csi_tc_trace); selects the TRACE instantiation
+  int debug;               // 8 + (first traced iteration << 8) + (traced CTA << 16); read by the TRACE instantiation only
   float act_scale, w_scale;  // power-of-two operand scalings (see csi_tc.cu)
 };
 
@@ -39,14 +39,10 @@ struct Launch {           // everything a potential launch needs
   float *net_y, *net_gx;        // y [n][4], gx [n][5]
   PeerX px;               // fused allreduce over peer memory (world <= 1: off)
   int sm_count;
-  // Gated sites (csi_potential_host): the copy engine fills io.z[] block by block while the kernel runs and
-  // publishes z_base + (stars copied so far) in *z_ready after each block; star i may be staged once
-  // *z_ready - z_base > i.  null = the sites are all there at launch.
-  const unsigned long long *z_ready;
-  unsigned long long z_base;
-  // hybrid: stars below z_direct_end are read from the caller's page-locked buffer itself (= io.z[] + z_host_delta
-  // floats, no gate), so the kernel starts at once while the copy engine works on the blocks behind them
-  long long z_direct_end, z_host_delta;
+  // Early exit (device-side NUTS, csi_nuts.cuh): when *stop != 0 the launch returns at once without touching
+  // anything -- a stopped sub-tree skips the leapfrogs queued behind it.  null = always run.
+  const int *stop;
+  int grid_limit;         // upper bound on the number of CTAs (0 = one per SM): several chains share one GPU
 };
 
 // returns the number of kernel launches issued (>0) or a negative cudaError
@@ -72,8 +68,6 @@ bool tc_supported(const csi_net &net);
 
 }  // namespace csi
 
-constexpr int kGateMaxBlocks = 64;  // star blocks of the gated host-buffer copy
-
 struct csi_handle {
   int device = 0, sm_count = 0, engine = 0;
   int level = 0, prior = 0;
@@ -98,13 +92,12 @@ struct csi_handle {
   double *h_out = nullptr, *d_out = nullptr;
   long long stage_len = 0;
   cudaStream_t stream = nullptr;
-  // gated host-buffer path: copy stream, progress word (device) and the values the copy engine writes into it
-  cudaStream_t copy_stream = nullptr;
-  unsigned long long *d_zflag = nullptr, *h_zflag_vals = nullptr;
-  unsigned long long zgate_base = 0;
-  bool zgate_on = false;
-  long long zgate_direct_end = 0, zgate_host_delta = 0;
   csi::PeerX px{};          // csi_set_peer_exchange
+  unsigned long long *d_epoch = nullptr;  // exchange epoch, advanced on the device by every exchange
+  const int *stop_flag = nullptr;         // Launch::stop of the next csi_potential (set by the NUTS driver)
+  int grid_limit = 0;
+  double *d_vec_partials = nullptr;         // scratch of the NUTS vector kernels (csi_nuts.cuh)
+  unsigned int *d_vec_counter = nullptr;
   long long last_launches = 0;
   int last_grid = 0, last_smem = 0;
 };

@@ -1,21 +1,66 @@
-// csi_reduce.cuh -- block reduce of the (U, hyper-gradient) partial sums and the single-pass grid reduce.
+// csi_reduce.cuh -- block reduce of the (U, hyper-gradient) partial sums, the single-pass grid reduce and the
+// allreduce over NVLink peer memory that the finalising block performs itself.
 #pragma once
 #include "csi_model.cuh"
 
 namespace csi {
 
-// Star-sharded evaluation: the allreduce of the 6 sums fused into the finalising block.  Every rank owns an
-// exchange buffer double[2][world][8] (epoch parity x source rank x {6 values, spare, flag}) that all ranks can
-// write over NVLink peer memory (csi_set_peer_exchange).  The finalising block stores its 6 sums + the epoch flag
-// into slot [epoch & 1][my rank] of EVERY rank's buffer, then waits for the world's flags in its own buffer and
-// adds the contributions in rank order (bit-identical totals on all ranks).  Double buffering by epoch parity is
-// enough: a rank can only be one evaluation ahead of the slowest one (it needs everybody's flag to finish).
+// Star-sharded evaluation: the allreduce of a handful of doubles fused into the finalising block of a kernel.
+// Every rank owns an exchange buffer double[2][world][kPxSlot] (epoch parity x source rank x {values, flag}) that
+// all ranks can write over NVLink peer memory (csi_set_peer_exchange).  The finalising block stores its sums + the
+// epoch flag into slot [epoch & 1][my rank] of EVERY rank's buffer, then waits for the world's flags in its own
+// buffer and adds the contributions in rank order (bit-identical totals on all ranks).  Double buffering by epoch
+// parity is enough: a rank can only be one exchange ahead of the slowest one (it needs everybody's flag to finish).
+// The epoch lives in device memory and is advanced by the exchange itself, so a launch replayed from a CUDA graph,
+// or skipped on every rank by the same device-side decision (Launch::stop), keeps the ranks in step.
 constexpr int kMaxPeers = 8;
+constexpr int kPxSlot = 32;  // doubles per slot: up to 31 values, the flag in the last one
 struct PeerX {
   double *bufs[kMaxPeers];
   int world, rank;
-  unsigned long long epoch;  // 1, 2, ...: number of this evaluation (same on all ranks)
+  unsigned long long *epoch;  // device word of this rank: exchanges completed so far (the same count on all ranks)
+  unsigned long long timeout_ns;  // how long a block waits for a peer before it poisons the result with NaN
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// vals[0..NV) (shared memory) <- sum over the ranks, in rank order.  Called by ALL threads of one block
+// (blockDim.x >= world); a peer that does not answer within px.timeout_ns poisons the result with NaN.
+template <int NV>
+__device__ __forceinline__ void peer_allreduce(const PeerX &px, double *vals) {
+  static_assert(NV < kPxSlot, "exchange slot");
+  __shared__ double got[kMaxPeers][NV];
+  const int tid = threadIdx.x;
+  __syncthreads();
+  const unsigned long long epoch = *reinterpret_cast<volatile unsigned long long *>(px.epoch) + 1ull;
+  const int par = (int)(epoch & 1ull);
+  if (tid < px.world) {
+    volatile double *dst = px.bufs[tid] + ((size_t)par * px.world + px.rank) * kPxSlot;
+    for (int j = 0; j < NV; ++j) dst[j] = vals[j];
+    __threadfence_system();
+    *reinterpret_cast<volatile unsigned long long *>(dst + kPxSlot - 1) = epoch;
+    volatile double *src = px.bufs[px.rank] + ((size_t)par * px.world + tid) * kPxSlot;
+    const volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(src + kPxSlot - 1);
+    const unsigned long long t0 = global_ns();
+    while (*flag != epoch && global_ns() - t0 < px.timeout_ns) {
+    }
+    __threadfence_system();
+    const bool ok = *flag == epoch;
+    for (int j = 0; j < NV; ++j) got[tid][j] = ok ? src[j] : nan("");
+  }
+  __syncthreads();
+  if (tid < NV) {
+    double t = 0.0;
+    for (int r = 0; r < px.world; ++r) t += got[r][tid];
+    vals[tid] = t;
+  }
+  if (tid == 0) *px.epoch = epoch;
+  __syncthreads();
+}
 
 // -------------------------------------------------------------------------------------------------
 // block reduce of the 6 partial sums + single-pass grid reduce (last block finalises, fixed order)
@@ -63,33 +108,7 @@ __device__ __noinline__ static void block_reduce_finalize(const DevModel &m, con
         tot[1 + j] = hier ? -(hon * (double)hv.gprior[j] + chain[j] * red_smem[1 + j]) : 0.0;
     }
     __syncthreads();
-    if (px.world > 1) {
-      // ---- fused allreduce over NVLink peer memory: thread p talks to rank p ----------------------------------
-      __shared__ double got[kMaxPeers][6];
-      const int par = (int)(px.epoch & 1ull);
-      if (tid < px.world) {
-        volatile double *dst = px.bufs[tid] + ((size_t)par * px.world + px.rank) * 8;
-        for (int j = 0; j < 6; ++j) dst[j] = tot[j];
-        __threadfence_system();
-        *reinterpret_cast<volatile unsigned long long *>(dst + 7) = px.epoch;
-        volatile double *src = px.bufs[px.rank] + ((size_t)par * px.world + tid) * 8;
-        const volatile unsigned long long *flag = reinterpret_cast<volatile unsigned long long *>(src + 7);
-        long long spins = 0;
-        while (*flag != px.epoch && ++spins < (1ll << 27)) {
-        }
-        __threadfence_system();
-        const bool ok = *flag == px.epoch;
-        for (int j = 0; j < 6; ++j) got[tid][j] = ok ? src[j] : nan("");  // a missing peer poisons the result
-      }
-      __syncthreads();
-      if (tid == 0)
-        for (int j = 0; j < 6; ++j) {
-          double t = 0.0;
-          for (int r = 0; r < px.world; ++r) t += got[r][j];
-          tot[j] = t;
-        }
-      __syncthreads();
-    }
+    if (px.world > 1) peer_allreduce<6>(px, tot);  // fused allreduce over NVLink peer memory
     if (tid == 0) {
       const bool hier = (m.prior_mode == P_HIER);
       for (int j = 0; j < 6; ++j) out6[j] = tot[j];
@@ -99,6 +118,5 @@ __device__ __noinline__ static void block_reduce_finalize(const DevModel &m, con
     }
   }
 }
-
 
 }  // namespace csi

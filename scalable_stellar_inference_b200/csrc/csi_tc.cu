@@ -94,7 +94,6 @@ struct __align__(128) Smem {
   unsigned short grid_lut[4][kLutBins];
   uint64_t w_full[2][2], w_empty[2][2], a_ready[2][2], d_ready[2], start_b;  // a_ready: one barrier per K-half
   uint32_t tmem_base;
-  long long z_seen;              // gated sites: the largest progress value any thread of the CTA has read
   double red[(kThreads / 32) * 6];
   HyperVals hv;
 };
@@ -254,9 +253,9 @@ __device__ __forceinline__ void issue_half(uint32_t d, uint32_t a_reg, uint32_t 
   }
 }
 
-// clock64 trace (CSI_TC_DEBUG & 8): recorder `who` of CTA 0 appends (tag, clock) pairs to its 1024-entry region
-// clock64 trace (CSI_TC_DEBUG=8).  The marks cost ~3.5 % of the kernel even when idle (a predicated store pair
-// and a counter per mark), so they exist only in the TRACE instantiation, which csi_tc_trace launches select.
+// clock64 trace (CSI_TC_DEBUG=8): a recorder appends (tag, clock) pairs to its 1024-entry region.  The marks cost
+// ~3.5 % of the kernel even when idle (a predicated store pair and a counter per mark), so they -- and every use of
+// TcWeights::debug -- exist only in the TRACE instantiation, which launches on a handle created under CSI_TC_DEBUG select.
 template <bool ON>
 struct Tracer {
   long long *p;
@@ -283,6 +282,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   extern __shared__ unsigned char smem_raw[];
   // align inside the shared window (keeps the pointer provably in the shared address space: LDS/STS, not LD/ST)
   Smem &S = *reinterpret_cast<Smem *>(smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u));
+  if (L.stop != nullptr && *reinterpret_cast<const volatile int *>(L.stop) != 0) return;  // skipped leapfrog (csi_nuts.cuh)
   const DevModel &m = L.model;
   const StarIO &io = L.io;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -296,7 +296,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   auto slot_iters = [&](int slot) { return (my_tiles + 1 - slot) / 2; };
 
   // CTA life-cycle marks of the traced CTA: 1 entry, 2 set-up done, 3 all tiles done, 4 reduction done
-  Tracer<TRACE> ctr{(L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ? L.tc.trace + 5 * 1024 : nullptr, 0};
+  Tracer<TRACE> ctr{nullptr, 0};
+  if constexpr (TRACE)
+    if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ctr.p = L.tc.trace + 5 * 1024;
   ctr.rec(1);
   // ---- one-time setup ----------------------------------------------------------------------------
   // Warp 11 initialises the barriers and evaluates the hyper-parameter terms (a ~3 k-cycle dependent chain behind
@@ -335,7 +337,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       ptx::mbar_init(&S.d_ready[b], 1);
     }
     ptx::mbar_init(&S.start_b, 1);
-    S.z_seen = 0;
     ptx::fence_barrier_init();
     HyperVals h{};
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
@@ -355,10 +356,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
-  if (L.tc.debug & 32) {  // timing experiment: CTAs start in four phases 8 us apart (de-phased PCIe staging bursts)
-    const long long t0 = clock64();
-    while (clock64() - t0 < (long long)(blockIdx.x & 3) * 14000) {}
-  }
   const uint32_t tmem = S.tmem_base;
   const HyperVals hv = S.hv;
   HyperAcc acc{};
@@ -378,7 +375,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         const int r = (int)(q % kNRing);
         const bool with_bias = hh == 0 && r < 5;  // only forward images carry a bias tile
         ptx::mbar_wait(&S.w_empty[t][hh], (uint32_t)((q & 1) ^ 1));
-        if ((L.tc.debug & 1) && q >= 1) { ptx::mbar_arrive(&S.w_full[t][hh]); continue; }  // timing experiment
         ptx::mbar_arrive_expect_tx(&S.w_full[t][hh], 2 * kHalfBytes + (with_bias ? kBiasBytes : 0u));
         const uint8_t *src = L.tc.img + (size_t)r * kStepBytes + (size_t)hh * kHalfBytes;
         ptx::bulk_g2s(&S.wring[t][hh][0], src, kHalfBytes, &S.w_full[t][hh]);
@@ -415,7 +411,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       while (!__all_sync(full, ptx::mbar_try_wait(bar, parity))) {
       }
     };
-    Tracer<TRACE> tr{(L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) ? L.tc.trace + 4 * 1024 : nullptr, 0};
+    Tracer<TRACE> tr{nullptr, 0};
+    if constexpr (TRACE)
+      if (L.tc.trace && blockIdx.x == 0 && lane == 0 && t == 0) tr.p = L.tc.trace + 4 * 1024;
     constexpr int kGateStage = FWD_ONLY ? 2 : 4;  // tile B starts when tile A's stage kGateStage is issued
     uint32_t k = 0, q = 0;            // stage counter of the tile's whole life (region parity); streamed-stage counter
     uint32_t apar0 = 0u, apar1 = 0u;  // parities of the next phases of a_ready[t][0 / 1]
@@ -500,8 +498,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     };
     Tracer<TRACE> tr{nullptr, 0};
     long long *tr_base = nullptr;  // trace of CTA (debug >> 16), starting at this slot's iteration (debug >> 8) & 255
-    if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
-      tr_base = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
+    if constexpr (TRACE)
+      if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && lane == 0 && (warp == 0 || warp == 3 || warp == 4 || warp == 7))
+        tr_base = L.tc.trace + (warp == 0 ? 0 : warp == 3 ? 1 : warp == 4 ? 2 : 3) * 1024;
     long long it = 0;
     // Start gate: tile B begins a quarter of an evaluation chain after tile A, so that the long CUDA-core phases
     // of one tile (priors; table gather + likelihood; gradient stores) run under the MMA stages of the other.
@@ -517,48 +516,20 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 #pragma unroll 4
       for (int j = 0; j < cnt; ++j) ptx::cp_async4(col + l.row[j] * kStageStride, l.src[j] + ii);
     };
-    // Gated sites (Launch::z_ready): wait until the copy engine has published star ii.  The CTA-wide S.z_seen keeps
-    // the polls to one per published block (stale values only cost another poll; progress is monotone).
-    auto wait_sites = [&](long long ii) {
-      if (NET || !L.z_ready || ii >= n) return;
-      volatile long long *seen = &S.z_seen;
-      if (*seen > ii) return;
-      long long v;
-      int spins = 0;
-      do {
-        v = (long long)(*reinterpret_cast<const volatile unsigned long long *>(L.z_ready) - L.z_base);
-      } while (v <= ii && ++spins < (1 << 20));  // bounded: a lost block shows up as a parity failure, not a hang
-      __threadfence_system();
-      *seen = v;
-    };
-    auto stage_sites = [&](long long ii) {
-      if (!L.z_ready) { stage(S.sites_list, ii); return; }
-      if (NET || ii >= n) return;
-      long long delta = 0;  // sites below z_direct_end come from the caller's buffer, the others from the gated copy
-      if (ii < L.z_direct_end) delta = L.z_host_delta; else wait_sites(ii);
-      const StageList &l = S.sites_list;
-      const int cnt = l.n;
-#pragma unroll 4
-      for (int j = 0; j < cnt; ++j)
-        ptx::cp_async4(col + l.row[j] * kStageStride, l.src[j] + ii + (l.row[j] < kSlots ? delta : 0));
-    };
+    auto stage_sites = [&](long long ii) { stage(S.sites_list, ii); };
     auto stage_obs = [&](long long ii) { stage(S.obs_list, ii); };
     if (my_iters > 0) stage_sites(((long long)blockIdx.x + t * gridDim.x) * kTile + row);
-    if (t == 1 && my_iters > 0 && !(L.tc.debug & 16)) ptx::mbar_wait(&S.start_b, 0u);
+    if (t == 1 && my_iters > 0) ptx::mbar_wait(&S.start_b, 0u);
     for (long long p = 0; p < my_iters; ++p) {
       const long long tile = (long long)blockIdx.x + (2 * p + t) * gridDim.x;
       const long long i = tile * kTile + row;
       const bool valid = i < n;
-      if (tr_base && p >= ((L.tc.debug >> 8) & 255)) tr.p = tr_base;
+      if constexpr (TRACE)
+        if (tr_base && p >= ((L.tc.debug >> 8) & 255)) tr.p = tr_base;
       const long long i_next = p + 1 < my_iters ? i + 2LL * kTile * gridDim.x : n;  // same row, this slot's next tile
       StarState st;
       float x[5];
-      if (valid && (L.tc.debug & 2)) {
-        st = StarState{};
-        st.x[0] = 0.3f; st.x[1] = 1.1f; st.x[2] = 0.1f; st.x[3] = 0.27f; st.x[4] = 2.0f; st.tau = 1.0f; st.dist = 100.f;
-#pragma unroll
-        for (int k = 0; k < 5; ++k) x[k] = (st.x[k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
-      } else if (valid && NET) {
+      if (valid && NET) {
 #pragma unroll
         for (int k = 0; k < 5; ++k) x[k] = (L.net_x[i * 5 + k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else if (valid) {
@@ -598,7 +569,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       tr.rec(504);
       publish_a(0);
       tr.rec(505);
-      if (!(L.tc.debug & 2)) stage_obs(i);  // the column is free: the priors hold the sites in registers
+      stage_obs(i);  // the column is free: the priors hold the sites in registers
 
       float un = 1.0f;    // cotangent un-scaling: true value = D * un
       float amax = 0.0f;  // max |A operand| of the current VJP stage (after scaling)
@@ -650,8 +621,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
               if (x_ == 0xdeadbeefu) tr.rec(999);
               tr.rec(602);
             }
-            if (L.tc.debug & 2) { g_o[0] = o[0]; g_o[1] = o[1]; g_o[2] = o[2]; g_o[3] = o[3]; }
-            else if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
+            if (BC == 0) { BcNone bc; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
             else if (BC == 1) { BcGrid bc{gl}; star_mid(m, io, i, st, o, g_o, bc, so, mo); }
             stage_sites(i_next);  // the observations have been consumed: the column takes the next tile's sites
             }
@@ -887,7 +857,8 @@ static int launch_tc_t(const Launch &L, cudaStream_t st, int *grid_out, int *sme
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return -(int)e;
   const long long n_tiles = (L.io.n + tc::kTile - 1) / tc::kTile;
-  const int grid = (int)std::min<long long>(n_tiles, L.sm_count);
+  const int ctas = L.grid_limit > 0 ? std::min(L.grid_limit, L.sm_count) : L.sm_count;
+  const int grid = (int)std::min<long long>(n_tiles, ctas);
   kern<<<grid, tc::kThreads, smem, st>>>(L);
   e = cudaGetLastError();
   if (e != cudaSuccess) return -(int)e;

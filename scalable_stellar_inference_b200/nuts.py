@@ -279,6 +279,128 @@ class NUTS:
         return out
 
 
+# ---------------------------------------------------------------------------------------------------------------
+# counter-based random numbers: the Python mirror of csi::nuts::hash_u64 (csrc/csi_nuts.cuh)
+# ---------------------------------------------------------------------------------------------------------------
+_M64 = (1 << 64) - 1
+K_MOMENTUM, K_DIRECTION, K_LEAF, K_MERGE = 1, 2, 3, 4
+
+
+def _mix64(x):
+    x ^= x >> 30
+    x = (x * 0xBF58476D1CE4E5B9) & _M64
+    x ^= x >> 27
+    x = (x * 0x94D049BB133111EB) & _M64
+    x ^= x >> 31
+    return x
+
+
+def hash_u64(seed, draw, kind, idx):
+    g = 0x9E3779B97F4A7C15
+    h = _mix64((seed + g) & _M64)
+    h = _mix64(h ^ ((draw + g) & _M64))
+    h = _mix64(h ^ ((kind * 0xD1B54A32D192ED03) & _M64))
+    return _mix64(h ^ ((idx + g) & _M64))
+
+
+def hash_uniform(seed, draw, kind, idx):
+    return (hash_u64(seed, draw, kind, idx) >> 11) * (1.0 / 9007199254740992.0)
+
+
+def leaf_to_ckpt(n):
+    """numpyro hmc_util._leaf_idx_to_ckpt_idxs: (idx_min, idx_max) of the checkpoints leaf n is tested against."""
+    idx_max = bin(n >> 1).count("1")
+    trailing = 0
+    while n & 1:
+        trailing += 1
+        n >>= 1
+    return idx_max - trailing + 1, idx_max
+
+
+class IterativeNUTS:
+    """Host restatement of the DEVICE sampler (csrc/csi_nuts.cuh), decision for decision: iterative sub-tree building
+    with checkpointed U-turn tests, in-place leapfrogs on the growing end, lazily copied sub-tree proposal, the same
+    hash stream for directions / leaf accepts / merges.  ``potential(z) -> (U, grad)`` on numpy vectors.  It is the
+    reference the GPU tests compare ``csi_nuts_transition`` with; momenta are passed in (the device draws its own)."""
+
+    def __init__(self, potential, seed=0, max_tree_depth=10, max_delta_energy=1000.0, dtype=np.float32):
+        self.potential, self.seed, self.max_depth, self.max_de = potential, int(seed), max_tree_depth, max_delta_energy
+        self.dtype = dtype
+
+    def transition(self, z, u, g, r0, inv_mass, eps, draw):
+        f = self.dtype
+        im = np.asarray(inv_mass, f)
+        dot = lambda a, b: float(np.dot(a.astype(np.float64), b.astype(np.float64)))  # noqa: E731
+        z_prop, g_prop, u_prop = np.array(z, f), np.array(g, f), float(u)
+        end = {+1: [z_prop.copy(), np.array(r0, f), g_prop.copy()], -1: [z_prop.copy(), np.array(r0, f), g_prop.copy()]}
+        r_sum = np.array(r0, f)
+        h0 = u_prop + 0.5 * dot(im * end[1][1], end[1][1])
+        logw_tree, sum_acc, n_prop, depth, turning, diverging = 0.0, 0.0, 0, 0, False, False
+        while depth < self.max_depth:
+            sign = +1 if (hash_u64(self.seed, draw, K_DIRECTION, depth) >> 63) else -1
+            e = f(sign * eps)
+            zc, rc, gc = end[sign]
+            ck_r, ck_rs = {}, {}
+            logw_sub, u_sub, z_sub, g_sub, r_sum_sub = -math.inf, u_prop, None, None, None
+            pending, stop, sub_turning = False, False, False
+            for leaf in range(1 << depth):
+                if pending:
+                    z_sub, g_sub = zc.copy(), gc.copy()
+                rc -= f(0.5) * e * gc
+                zc += e * (im * rc)
+                u1, g1 = self.potential(zc)
+                gc[:] = np.asarray(g1, f)
+                rc -= f(0.5) * e * gc
+                kin = 0.5 * dot(im * rc, rc)
+                r_sum_sub = rc.copy() if leaf == 0 else r_sum_sub + rc
+                idx_min, idx_max = leaf_to_ckpt(leaf)
+                if leaf % 2 == 0:
+                    ck_r[idx_max], ck_rs[idx_max] = rc.copy(), r_sum_sub.copy()
+                de = (u1 + kin) - h0
+                if not math.isfinite(de):
+                    de = math.inf
+                w = -de
+                div = de > self.max_de
+                sum_acc += min(1.0, math.exp(-de)) if de < math.inf else 0.0
+                n_prop += 1
+                if leaf == 0:
+                    take, logw_sub = True, w
+                else:
+                    p = 0.0 if w == -math.inf else 1.0 / (1.0 + math.exp(min(logw_sub - w, 700.0)))
+                    take = hash_uniform(self.seed, draw, K_LEAF, (depth << 32) | leaf) < p
+                    logw_sub = _logaddexp(logw_sub, w)
+                pending = take
+                if take:
+                    u_sub = u1
+                turn = False
+                for c in range(idx_max, idx_min - 1, -1):
+                    sub = r_sum_sub - ck_rs[c] + ck_r[c]
+                    cen = sub - f(0.5) * (ck_r[c] + rc)
+                    turn = turn or dot(im * ck_r[c], cen) <= 0.0 or dot(im * rc, cen) <= 0.0
+                diverging = diverging or div
+                sub_turning = sub_turning or turn
+                if div or turn:
+                    stop = True
+                    break
+            depth += 1
+            if stop:
+                turning = turning or sub_turning
+                break
+            p = min(1.0, math.exp(min(logw_sub - logw_tree, 0.0)))
+            if hash_uniform(self.seed, draw, K_MERGE, depth - 1) < p:
+                z_prop, g_prop = (zc.copy(), gc.copy()) if pending else (z_sub.copy(), g_sub.copy())
+                u_prop = u_sub
+            logw_tree = _logaddexp(logw_tree, logw_sub)
+            r_sum = r_sum + r_sum_sub
+            rl, rr = end[-1][1], end[+1][1]
+            cen = r_sum - f(0.5) * (rl + rr)
+            if dot(im * rl, cen) <= 0.0 or dot(im * rr, cen) <= 0.0:
+                turning = True
+                break
+        return dict(z=z_prop, g=g_prop, u=u_prop, accept=sum_acc / max(n_prop, 1), depth=depth, n_leapfrog=n_prop,
+                    diverging=diverging, turning=turning, h0=h0)
+
+
 def effective_sample_size(x):
     """Bulk ESS of draws x[chain, draw] (Geyer initial monotone sequence on split chains; the estimator of
     numpyro.diagnostics.effective_sample_size / Stan)."""
@@ -370,13 +492,164 @@ class DevicePotential:
         return float(d[0]) + float(d[2]), float(d[1]) + float(d[3])
 
 
-def sample_model(model, z0_flat, num_warmup, num_samples, seed=0, group=None, rank=0, world=1, collect=None, **kw):
-    """NUTS over a conditioned (and, for world > 1, sharded) model; returns the run dict with hyper-site draws."""
+class DeviceNUTS:
+    """One chain with the tree logic on the device (``csi_nuts_*``, csrc/csi_nuts.cuh): a transition costs one host
+    synchronisation per doubling, a leapfrog three stream-ordered launches inside a CUDA graph.  Adaptation follows
+    numpyro's warm-up as the reference configures it (scripts/model_star.py:18-22): dual-averaging step size to
+    ``target_accept_prob`` 0.8, ``find_heuristic_step_size``, regularised diagonal mass matrix in Stan windows.
+
+    ``model`` must be conditioned (and, for ``world > 1``, sharded with the peer exchange switched on); the state
+    vectors are torch tensors only because PyTorch owns the device memory."""
+
+    def __init__(self, model, z0_flat, seed=0, target_accept=0.8, max_tree_depth=10, max_delta_energy=1000.0,
+                 adapt_mass=True, star_offset=0, n_total=None):
+        import ctypes as C
+        from . import _lib
+        self.C, self._lib = C, _lib
+        self.lib, self.model = model._lib, model
+        self.dev = torch.device("cuda", model.device)
+        self.nh = len(model.hyper_sites)
+        self.target, self.adapt_mass, self.seed = target_accept, adapt_mass, int(seed)
+        self.z = torch.as_tensor(np.asarray(z0_flat, np.float32), device=self.dev).contiguous()
+        self.g = torch.zeros_like(self.z)
+        self.inv_mass = torch.ones_like(self.z)
+        h = C.c_void_p()
+        n_total = model.n_local if n_total is None else n_total
+        torch.cuda.synchronize(self.dev)
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.csi_nuts_create(model._h, self.z.data_ptr(), self.g.data_ptr(), self.inv_mass.data_ptr(),
+                                                max_tree_depth, float(max_delta_energy), self.seed, int(star_offset),
+                                                int(n_total), C.byref(h)))
+        self._s = h
+        self.draw = 0
+        self.n_evals = self.n_evals_warmup = 0
+        self.launches = self.host_syncs = 0
+        u = C.c_double()
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.csi_nuts_init_state(self._s, C.byref(u)))
+        self.u = u.value
+        self.n_evals += 1
+
+    def __del__(self):
+        if getattr(self, "_s", None):
+            self.lib.csi_nuts_destroy(self._s)
+            self._s = None
+
+    def transition(self, step_size):
+        st = self._lib.NutsStats()
+        with torch.cuda.device(self.dev):
+            self._lib.check(self.lib.csi_nuts_transition(self._s, float(step_size), self.draw, self.C.byref(st)))
+        self.draw += 1
+        self.u = st.potential
+        self.n_evals += st.num_leapfrog
+        self.launches += st.launches
+        self.host_syncs += st.host_syncs
+        return st
+
+    def probe(self, step_size):
+        de = self.C.c_double()
+        with torch.cuda.device(self.dev):
+            self._lib.check(self.lib.csi_nuts_probe_step(self._s, float(step_size), self.draw, self.C.byref(de)))
+        self.draw += 1
+        self.n_evals += 1
+        return de.value
+
+    def find_heuristic_step_size(self, step_size=1.0):
+        log_target = math.log(self.target)
+        direction = 0
+        for _ in range(60):
+            de = self.probe(step_size)
+            new_dir = 1 if (math.isfinite(de) and -de > log_target) else -1
+            if direction and new_dir != direction:
+                break
+            direction = new_dir
+            step_size *= 2.0 ** direction
+            if not (1e-10 < step_size < 1e10):
+                break
+        return step_size
+
+    def run(self, num_warmup, num_samples, collect=None, progress=None, step_size=None):
+        nh = self.nh
+        collect = collect or (lambda z: z[:max(nh, 1)].detach().double().cpu().numpy().copy())
+        if not math.isfinite(self.u):
+            raise ValueError("non-finite potential at the initial point")
+        step = self.find_heuristic_step_size() if step_size is None else step_size
+        t0, kappa, gamma = 10.0, 0.75, 0.05
+        da = dict(mu=math.log(10.0 * step), x_bar=0.0, h_bar=0.0, t=0)
+        windows = NUTS.adaptation_windows(num_warmup) if self.adapt_mass else []
+        ends = {e: s for s, e in windows}
+        in_window = lambda i: any(s <= i < e for s, e in windows)  # noqa: E731
+        z = self.z
+        w_n, w_mean, w_m2 = 0, torch.zeros_like(z, dtype=torch.float64), torch.zeros_like(z, dtype=torch.float64)
+        out = dict(samples=[], accept=[], depth=[], diverging=[], potential=[], n_leapfrog=[])
+        for it in range(num_warmup + num_samples):
+            warm = it < num_warmup
+            st = self.transition(step)
+            acc = st.accept_prob
+            if warm:
+                da["t"] += 1
+                t = da["t"]
+                da["h_bar"] = (1 - 1 / (t + t0)) * da["h_bar"] + (self.target - acc) / (t + t0)
+                x = da["mu"] - math.sqrt(t) / gamma * da["h_bar"]
+                eta = t ** (-kappa)
+                da["x_bar"] = eta * x + (1 - eta) * da["x_bar"]
+                step = math.exp(x)
+                if in_window(it):
+                    w_n += 1
+                    d = z.double() - w_mean
+                    w_mean += d / w_n
+                    w_m2 += d * (z.double() - w_mean)
+                if (it + 1) in ends and w_n > 1:
+                    var = w_m2 / (w_n - 1)
+                    var = var * (w_n / (w_n + 5.0)) + 1e-3 * (5.0 / (w_n + 5.0))      # Stan's regularisation
+                    self.inv_mass.copy_(var.to(z.dtype))
+                    w_n = 0; w_mean.zero_(); w_m2.zero_()
+                    torch.cuda.current_stream(self.dev).synchronize()
+                    step = self.find_heuristic_step_size(math.exp(da["x_bar"]))
+                    da = dict(mu=math.log(10.0 * step), x_bar=0.0, h_bar=0.0, t=0)
+                if it + 1 == num_warmup:
+                    step = math.exp(da["x_bar"]) if da["t"] > 0 else step
+                    self.n_evals_warmup = self.n_evals
+                # the adaptation arithmetic above ran on torch's stream, the sampler has its own: the next
+                # transition must not overwrite z / read inv_mass before those kernels are done
+                torch.cuda.current_stream(self.dev).synchronize()
+            else:
+                out["samples"].append(collect(z))
+                out["accept"].append(acc); out["depth"].append(st.depth); out["diverging"].append(bool(st.diverging))
+                out["potential"].append(st.potential); out["n_leapfrog"].append(st.num_leapfrog)
+            if progress:
+                progress(it, warm, step, st.depth, acc)
+        out.update(step_size=step, n_evals=self.n_evals, n_evals_warmup=self.n_evals_warmup, z_last=z,
+                   launches=self.launches, host_syncs=self.host_syncs)
+        return out
+
+
+def split_rhat(x):
+    """Split-chain potential scale reduction of draws x[chain, draw] (Gelman et al.; numpyro.diagnostics.split_gelman_rubin)."""
+    x = np.asarray(x, np.float64)
+    if x.ndim == 1:
+        x = x[None]
+    half = x.shape[1] // 2
+    x = np.concatenate([x[:, :half], x[:, half:2 * half]], axis=0)
+    n = x.shape[1]
+    w = x.var(axis=1, ddof=1).mean()
+    b = n * x.mean(axis=1).var(ddof=1)
+    return float(math.sqrt(((n - 1) / n * w + b / n) / w)) if w > 0 else float("nan")
+
+
+def sample_model(model, z0_flat, num_warmup, num_samples, seed=0, group=None, rank=0, world=1, collect=None,
+                 device_tree=True, star_offset=0, n_total=None, progress=None, **kw):
+    """NUTS over a conditioned (and, for world > 1, sharded) model; returns the run dict with hyper-site draws.
+    ``device_tree=True`` (default): the device-side sampler ``DeviceNUTS``; False: the host-recursive ``NUTS`` with
+    one synchronisation per leapfrog (round 1's driver, kept as a cross-check)."""
+    if device_tree:
+        nuts = DeviceNUTS(model, z0_flat, seed=seed, star_offset=star_offset, n_total=n_total, **kw)
+        return nuts.run(num_warmup, num_samples, collect=collect, progress=progress)
     dev = torch.device("cuda", model.device)
     pot = DevicePotential(model, group)
     space = VectorSpace(n_hyper=pot.nh, group=group, sharded=world > 1)
     nuts = NUTS(pot, space, seed=seed, rank=rank, **kw)
     z0 = torch.as_tensor(np.asarray(z0_flat, dtype=np.float32), device=dev)
-    out = nuts.run(z0, num_warmup, num_samples, collect=collect)
+    out = nuts.run(z0, num_warmup, num_samples, collect=collect, progress=progress)
     out["n_evals_warmup"] = getattr(nuts, "n_evals_warmup", 0)
     return out

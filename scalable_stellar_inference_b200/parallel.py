@@ -128,7 +128,8 @@ def setup_peer_exchange(model, group=None):
         if world < 2 or world > 8:
             return None
         dev = torch.device("cuda", model.device)
-        n = 2 * world * 8
+        from ._lib import PEER_SLOT_DOUBLES
+        n = 2 * world * PEER_SLOT_DOUBLES          # CSI_PEER_BUF_DOUBLES(world), include/csi.h
         buf = symm_mem.empty(n, dtype=torch.float64, device=dev)
         buf.zero_()
         hdl = symm_mem.rendezvous(buf, group if group is not None else dist.group.WORLD)

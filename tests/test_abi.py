@@ -36,19 +36,19 @@ def test_every_declared_symbol_is_exported(lib):
     assert not missing, missing
     assert set(lib.EXPORTS) == set(names), set(lib.EXPORTS) ^ set(names)
     handle = lib.load()
-    assert handle.csi_version() == 100
+    assert handle.csi_version() == 200
 
 
 def test_struct_layout_matches_header(lib, tmp_path):
     src = tmp_path / "sz.c"
     src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "csi.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu\\n",'
                    'sizeof(csi_config),sizeof(csi_net),sizeof(csi_grid),sizeof(csi_tn),offsetof(csi_config,emulator),'
-                   'offsetof(csi_config,device));return 0;}\n')
+                   'offsetof(csi_config,device));printf("%zu %zu\\n",sizeof(csi_nuts_stats),offsetof(csi_nuts_stats,depth));return 0;}\n')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
     got = [int(t) for t in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
     want = [C.sizeof(lib.Config), C.sizeof(lib.Net), C.sizeof(lib.Grid), C.sizeof(lib.Tn), lib.Config.emulator.offset,
-            lib.Config.device.offset]
+            lib.Config.device.offset, C.sizeof(lib.NutsStats), lib.NutsStats.depth.offset]
     assert got == want
 
 

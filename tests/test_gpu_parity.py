@@ -68,6 +68,8 @@ def test_no_diag_no_mh_arrays():
         assert abs(u - u_ref) <= 1e-5 * abs(u_ref)
         for k in spec.star_sites():
             l2 = np.linalg.norm(g[k] - g_ref[k]) / np.linalg.norm(g_ref[k])
+            # ALL 300 stars, kink-ambiguous ones included (check_parity's all-star guard is 2e-2): one star on the
+            # wrong side of a ReLU kink costs ~1e-3 of the norm at this size
             assert l2 < 2e-3, (k, l2)
 
 
@@ -86,6 +88,8 @@ def test_engines_agree_and_deterministic():
     ob, gb = res["tcgen05"]
     assert abs(oa[0] - ob[0]) <= 5e-6 * abs(oa[0]), (oa[0], ob[0])
     np.testing.assert_allclose(oa[1:], ob[1:], rtol=1e-5, atol=1e-5 * np.abs(oa[1:]).max())
+    # all 5000 stars, kink-ambiguous ones included: the engines round pre-activations differently, so a handful of
+    # stars legitimately land on different sides of a ReLU kink (each costs ~1e-4 of the norm here)
     assert np.linalg.norm(ga - gb) <= 1e-3 * np.linalg.norm(ga)
 
 
@@ -127,34 +131,66 @@ def test_out_of_grid_is_nan_not_error():
     assert np.isnan(u)
 
 
-@pytest.mark.parametrize("n", [100_000, 1_000_000])
-def test_full_size_properties(n):
-    """BASELINE sizes (configs 4/5): finite, deterministic, and additive over star blocks.  The oracle is only
-    run on a 2000-star slice of the same problem."""
-    import scalable_stellar_inference_b200 as ssi
-    rng = np.random.default_rng(3)
-    name = "hier_diag_seis"
-    m0 = 2000
-    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, m0)
-    reps = n // m0
-    tile = lambda a: np.tile(np.asarray(a), (reps,) + (1,) * (np.ndim(a) - 1))  # noqa: E731
-    zb = {k: (v if np.ndim(v) == 0 else tile(v)) for k, v in z0.items()}
-    model = ssi.HierarchicalStarModel(n, PU.CASES[name]["obs"]).condition(tile(obs), tile(diag), M_H_loc=tile(ml), M_H_scale=tile(ms))
-    zf = model.flatten(zb)
+FULL_SIZE = [("hier_phot_grid", 1_000_000), ("hier_diag_seis", 100_000), ("hier_diag", 10_000), ("multi_phot_grid", 1_000)]
+
+
+@pytest.mark.parametrize("name,n", FULL_SIZE)
+def test_full_size_against_oracle_windows(name, n):
+    """Every BASELINE configuration at its stated size, NON-tiled synthetic stars (synthetic.make_problem draws each
+    star on its own): config 4 = hier_phot_grid at 1 M (the launch bench.py times), config 5 = hier_diag_seis at
+    100 k, config 3 = hier_diag at 10 k, config 2 = multi_phot_grid at 1 k.  The fp64 oracle cannot run a million
+    stars in test time, so it is run on 2 000-star WINDOWS of the same population -- the first stars, the last ones
+    (partial tile), one straddling the boundary between two tile rounds of the persistent kernel (148 CTAs x 128
+    stars), and random ones -- and compared, under the standard check_parity bounds, with a window-sized launch at
+    the same hyper-parameters; the full-size launch must then reproduce those per-star gradients BIT FOR BIT (a
+    star's arithmetic does not depend on its tile mates, its CTA, its tile slot or the staging-column history), be
+    finite everywhere, deterministic, and its U must equal the sum over 8 contiguous shards (csi_set_shard)."""
+    from scalable_stellar_inference_b200 import synthetic
+    spec0 = PU.oracle_spec(name, n)
+    model = PU.product_model(name, n, "tcgen05")
+    z0, obs, diag, ml, ms, _ = synthetic.make_problem(model, n)
+    z0 = PU.f32_point(z0)
+    model.condition(obs, diag, M_H_loc=ml, M_H_scale=ms)
+    zf = model.flatten(z0)
     o1, g1 = model.potential_and_grad_flat(zf)
     o2, g2 = model.potential_and_grad_flat(zf)
     assert np.all(np.isfinite(o1)) and np.all(np.isfinite(g1))
     assert np.array_equal(o1, o2) and np.array_equal(g1, g2)
-    # additivity: the tiled problem is `reps` copies of the slice -> star terms scale linearly
-    u_ref, g_ref, terms = M.potential_and_grad(spec, z0, obs, diag, ml, ms, return_terms=True)
-    u_expect = -(terms["hyper_logp"] + reps * float(np.sum(terms["per_star"])))
-    assert abs(o1[0] - u_expect) <= 1e-5 * abs(u_expect)
-    gd = model.unflatten(g1)
-    for k in spec.star_sites():
-        blocks = gd[k].reshape(reps, m0)
-        assert np.array_equal(blocks[0], blocks[-1]) and np.array_equal(blocks[0], blocks[reps // 2])
-        l2 = np.linalg.norm(blocks[0] - g_ref[k]) / np.linalg.norm(g_ref[k])
-        assert l2 <= 2e-3, (k, l2)
+    gfull = model.unflatten(g1)
+    hyper = spec0.hyper_sites()
+    w = min(2000, n)
+    rng = np.random.default_rng(5)
+    round_stars = 148 * 128
+    starts = {0, n - w}
+    if n > 2 * round_stars:
+        starts |= {2 * round_stars - w // 2, round_stars - 77}
+        starts |= {int(v) for v in rng.integers(0, n - w, 2)}
+    amb = []
+    for lo in sorted(starts):
+        sl = slice(lo, lo + w)
+        zw = {k: (v if np.ndim(v) == 0 else np.asarray(v)[sl]) for k, v in z0.items()}
+        spec = PU.oracle_spec(name, w)
+        prob = (zw, obs[sl], diag[sl], ml[sl], ms[sl])
+        u_ref, g_ref = M.potential_and_grad(spec, *prob)
+        mw = PU.product_model(name, w, "tcgen05").condition(obs[sl], diag[sl], M_H_loc=ml[sl], M_H_scale=ms[sl])
+        u, g = mw.potential_and_grad(zw)
+        rep = PU.check_parity(name, w, u, g, u_ref, g_ref, prob, hyper, spec.star_sites())
+        amb.append(rep["ambiguous_frac"])
+        for k in spec.star_sites():
+            assert np.array_equal(np.asarray(g[k]), gfull[k][sl]), (name, lo, k)
+    assert max(amb) <= 0.02, amb   # kink-ambiguous stars are excluded from the L2 criterion: keep them rare
+    print(name, n, "windows", sorted(starts), "ambiguous_frac", [f"{a:.4f}" for a in amb])
+    if hyper:   # shard additivity at full size (8 contiguous shards, hyper-prior on shard 0 only)
+        tot = np.zeros(6)
+        from scalable_stellar_inference_b200.parallel import shard_problem
+        for r in range(8):
+            m = PU.product_model(name, n, "tcgen05").set_shard(r, 8)
+            zl, ol, dl, mll, msl = shard_problem(z0, obs, diag, ml, ms, r, 8)
+            m.condition(ol, dl, M_H_loc=mll, M_H_scale=msl)
+            o, _ = m.potential_and_grad_flat(m.flatten(zl))
+            tot += o
+            del m
+        np.testing.assert_allclose(tot, o1, rtol=1e-9, atol=1e-9 * np.abs(o1).max())
 
 
 @pytest.mark.gpu
@@ -207,34 +243,3 @@ def test_zero_copy_host_potential_is_bit_identical_to_device_buffers(engine):
         assert u == out[0] and np.array_equal(gh, out[1:6])
         assert np.array_equal(zc.grad_pin.numpy()[5:], np.asarray(grad)[5:])
     assert zc.h2d_bytes == zf.size * 4 and zc.launches == 3
-
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("gate", ["1", "2", "3", "4"])
-def test_gated_host_sites_copy_is_bit_identical_to_device_buffers(gate, monkeypatch):
-    """csi_potential_host on page-locked buffers with CSI_HOST_GATE = 1 / 2 (opt-in; launches of >= 8 tile rounds): the copy engine brings the sites in
-    star blocks while the kernel runs and the kernel stages a tile only once its block has been published
-    (Launch::z_ready).  A different z every call, so a tile staged before its block landed would read the previous
-    call's sites; potential, hyper-gradient and per-star gradient must equal the device-buffer evaluation bit for bit."""
-    from scalable_stellar_inference_b200.parallel import ZeroCopyHostPotential
-    monkeypatch.setenv("CSI_HOST_GATE", gate)
-    monkeypatch.setenv("CSI_HOST_GATE_DIRECT", "3")  # mode 3: the first 3 rounds straight from the caller's buffer
-    name, n = "hier_phot_grid", 230_000
-    spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, 1000)
-    rep = n // 1000
-    tile = lambda a: np.tile(np.asarray(a), (rep,) + (1,) * (np.ndim(a) - 1))  # noqa: E731
-    zb = {k: (v if np.ndim(v) == 0 else tile(v)) for k, v in z0.items()}
-    model = PU.product_model(name, n, "tcgen05").condition(tile(obs), tile(diag), M_H_loc=tile(ml), M_H_scale=tile(ms))
-    assert n >= 8 * 128 * model.info()["sm_count"], "the launch must be long enough for the gated path"
-    zf = np.asarray(model.flatten(zb), np.float32)
-    zc = ZeroCopyHostPotential(model)
-    wiggle = np.sin(np.arange(zf.size - 5, dtype=np.float64)).astype(np.float32)
-    for k in range(4):
-        zk = zf.copy()
-        zk[5:] += np.float32(2e-3 * k) * wiggle
-        out, grad = model.potential_and_grad_flat(zk)
-        zc.load(zk)
-        zc.grad_pin.zero_()
-        u, gh, gview = zc.value_and_grad_host()
-        assert np.isfinite(u) and u == out[0] and np.array_equal(gh, out[1:6])
-        assert np.array_equal(zc.grad_pin.numpy()[5:], np.asarray(grad)[5:], equal_nan=True)

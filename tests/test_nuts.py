@@ -129,3 +129,51 @@ def test_fused_leapfrog_and_uturn_kernels_match_the_vector_ops(name, n):
     a_ref = float(torch.dot((im * r_left).double(), rc)); b_ref = float(torch.dot((im * r_right).double(), rc))
     a, b = pot.uturn(r_left, r_right, r_sum, im)
     assert a == pytest.approx(a_ref, rel=1e-6, abs=1e-6 * n) and b == pytest.approx(b_ref, rel=1e-6, abs=1e-6 * n)
+
+
+def test_hash_mirror_matches_libcsi():
+    """nuts.hash_u64 (Python) == csi::nuts::hash_u64 (the stream behind every device-side decision)."""
+    from scalable_stellar_inference_b200 import _lib, nuts
+    lib = _lib.load()
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        a = [int(v) for v in rng.integers(0, 2 ** 63, 4)]
+        a[2] = a[2] % 5
+        assert lib.csi_nuts_hash(*a) == nuts.hash_u64(*a)
+    u = [nuts.hash_uniform(7, d, nuts.K_LEAF, 5) for d in range(4000)]
+    assert 0.0 <= min(u) and max(u) < 1.0 and abs(np.mean(u) - 0.5) < 0.02
+
+
+def test_leaf_to_checkpoint_indices():
+    from scalable_stellar_inference_b200.nuts import leaf_to_ckpt
+    # numpyro hmc_util._leaf_idx_to_ckpt_idxs docstring examples: 6 -> idx_max 2, no test; 7 -> 3 sub-trees; 13 -> 1
+    assert leaf_to_ckpt(6) == (3, 2) and leaf_to_ckpt(7) == (0, 2) and leaf_to_ckpt(13) == (2, 2)
+    assert leaf_to_ckpt(0) == (1, 0) and leaf_to_ckpt(1) == (0, 0)
+
+
+def test_iterative_nuts_samples_a_gaussian():
+    """The host restatement of the device sampler (IterativeNUTS) targets the right distribution: fixed step size,
+    correlated scales, moments within Monte-Carlo error; trajectories stop by U-turn, not by depth."""
+    from scalable_stellar_inference_b200.nuts import IterativeNUTS
+    d = 10
+    sig = np.linspace(0.3, 2.0, d)
+
+    def pot(z):
+        z = np.asarray(z, np.float64)
+        return float(0.5 * np.sum(z ** 2 / sig ** 2)), z / sig ** 2
+
+    rng = np.random.default_rng(4)
+    nuts = IterativeNUTS(pot, seed=9, max_tree_depth=8, dtype=np.float64)
+    z = np.full(d, 0.2)
+    u, g = pot(z)
+    im = np.ones(d)
+    draws, depth, acc = [], [], []
+    for t in range(1500):
+        out = nuts.transition(z, u, g, rng.standard_normal(d), im, 0.25, t)
+        z, u, g = out["z"], out["u"], out["g"]
+        draws.append(z.copy()); depth.append(out["depth"]); acc.append(out["accept"])
+    s = np.array(draws[200:])
+    ess = np.array([effective_sample_size(s[:, k]) for k in range(d)])
+    assert np.all(np.abs(s.mean(0)) < 5 * sig / np.sqrt(ess))
+    assert np.all(np.abs(s.std(0) / sig - 1) < 0.15)
+    assert 2 <= np.mean(depth) < 7.5 and np.mean(acc) > 0.7
