@@ -1,16 +1,19 @@
 #!/usr/bin/env python
-"""bench.py -- logp+grad evaluations/s of the hierarchical spec+phot model (BASELINE.json config 4: 1 M synthetic
-stars, observables log_Teff, log_g, G/BP/RP magnitudes, parallax; BC table interpolation), star axis sharded over
-N GPUs with one 6-double allreduce per evaluation.
+"""bench.py -- logp+grad evaluations/s of celestify's star models on the B200 path, one BASELINE.json configuration
+per run (default: config 4, the one the metric is quoted on: hierarchical spec+phot, 1 M synthetic stars, BC table,
+star axis sharded over N GPUs with one 6-double exchange per evaluation).
 
-    python bench.py --gpus 1 --steps 20 --warmup 3
+    python bench.py --gpus 1 --steps 20 --warmup 3                 # config 4
+    python bench.py --config c2|c3|c4|c5 ...                       # the other BASELINE configurations
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus 8 --steps 20 --warmup 3
     python bench.py --impl reference ...      # CPU restatement of the reference on the host cores
 
 One "step" = one evaluation of U(z) and dU/dz for ALL stars (the thing numpyro's NUTS calls per leapfrog).
-value = evaluations/s with z resident in HBM; e2e = the same through ShardedPotential.value_and_grad_host
-(pinned host z -> device, evaluate, allreduce, gradient + U back to the host, every step).
+value = evaluations/s with z resident in HBM; e2e = the same from / to page-locked HOST buffers through the C ABI
+(csi_potential on the buffers' device aliases: the kernel reads the sites and writes the gradient over PCIe itself),
+K steps queued back to back and one host synchronisation at the end, as a device-side sampler drives it;
+e2e.sync_per_step is the same with a host synchronisation after every step (csi_potential_host).
 """
 from __future__ import annotations
 
@@ -28,11 +31,25 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-OBSERVABLES = ["log_Teff", "log_g", "mag", "plx"]
 BANDS = ["G", "BP", "RP"]
 FLOP_PER_STAR = 332_288          # emulator fwd + input-VJP (SURVEY 8d / BASELINE.md section 3)
 HIDDEN_FLOP_PER_STAR = 327_680   # the 10 tensor-core contractions
 MMA_PASSES = 3
+
+# BASELINE.json configs[1..4] (configs[0] is the reference's single-star CPU smoke case: a parity test, not a bench line)
+CONFIGS = {
+    "c2": dict(level="multi", obs=["mag", "plx"], phot=True, stars=1_000,
+               text="BASELINE config 2: MultiStarModel photometric, observables [mag(G,BP,RP), plx], kind=diag, BC table "
+                    "70x26x18x13 (synthetic MIST stand-in)"),
+    "c3": dict(level="hierarchical", obs=["log_Teff", "log_g"], phot=False, stars=10_000,
+               text="BASELINE config 3: HierarchicalStarModel spectroscopic, observables [log_Teff, log_g], kind=diag"),
+    "c4": dict(level="hierarchical", obs=["log_Teff", "log_g", "mag", "plx"], phot=True, stars=1_000_000,
+               text="BASELINE config 4: HierarchicalStarModel spec+phot, observables [log_Teff, log_g, mag(G,BP,RP), plx], "
+                    "kind=diag, BC table 70x26x18x13 (synthetic MIST stand-in)"),
+    "c5": dict(level="hierarchical", obs=["log_Teff", "log_L", "log_Dnu", "log_numax"], phot=False, stars=100_000,
+               text="BASELINE config 5: HierarchicalStarModel with asteroseismic likelihood, observables [log_Teff, log_L, "
+                    "log_Dnu, log_numax], kind=diag"),
+}
 
 
 def parse():
@@ -41,9 +58,11 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--stars", type=int, default=1_000_000)
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
+    ap.add_argument("--stars", type=int, default=0, help="override the configuration's star count")
     ap.add_argument("--engine", default="tcgen05", choices=["tcgen05", "ffma"])
-    ap.add_argument("--cpu-sample", type=int, default=20_000)
+    ap.add_argument("--cpu-budget", type=float, default=20.0, help="seconds of CPU work for the in-line cpu_baseline")
+    ap.add_argument("--ref-budget", type=float, default=240.0, help="seconds the --impl reference run may take")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--nccl-allreduce", action="store_true", help="keep the NCCL allreduce instead of the in-kernel exchange")
@@ -53,7 +72,11 @@ def parse():
                          "star blocks with explicit H2D / D2H copies on streams")
     ap.add_argument("--e2e-equal", action="store_true", help="equal star blocks instead of the triangular ramp")
     ap.add_argument("--e2e-no-graph", action="store_true", help="issue the host-buffer path per call, no CUDA graph")
-    return ap.parse_args()
+    a = ap.parse_args()
+    a.cfg = CONFIGS[a.config]
+    if a.stars <= 0:
+        a.stars = a.cfg["stars"]
+    return a
 
 
 def measured_peaks():
@@ -72,6 +95,14 @@ def ncu_traffic():
         return None, None
     d = json.load(open(p))
     return d.get("dram_read_bytes", 0) + d.get("dram_write_bytes", 0), d
+
+
+def git_sha(path):
+    try:
+        return subprocess.run(["git", "log", "-1", "--format=%h", "--", path], cwd=ROOT, capture_output=True,
+                              text=True).stdout.strip() or None
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -116,58 +147,137 @@ class ClockSampler(threading.Thread):
 # ---------------------------------------------------------------------------------------------------------------
 # CPU legs (the ONLY places that touch oracle/)
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_reference_rate(n_total, sample, budget_s=20.0, steps=None, warmup=2):
-    """Times the CPU restatement of the reference (oracle port: numpy, fp32 emulator as in the reference's default
-    precision, BLAS on all host cores) on `sample` stars of the same workload; returns evals/s extrapolated to
-    n_total stars (cost is linear in stars) and a description."""
-    from oracle import model as M, synth
-    from oracle.bc import GridInterpolator, synthetic_grid
-    from oracle.nets import load_emulator
-    spec = M.ModelSpec("hierarchical", sample, list(OBSERVABLES), bands=3, bc=GridInterpolator(*synthetic_grid()),
-                       bc_mode="grid", emulator=load_emulator(np.float32))
-    z0, obs, diag, ml, ms = synth.make_problem(spec)
-    for _ in range(warmup):
-        M.potential_and_grad(spec, z0, obs, diag, ml, ms)
-    times = []
-    t_start = time.perf_counter()
-    while True:
+def host_threads():
+    """Every host core this process may use -- set explicitly (torch.distributed.run exports OMP_NUM_THREADS=1,
+    which would otherwise single-thread BLAS and torch without anybody noticing)."""
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count() or 1
+    import torch
+    torch.set_num_threads(cores)
+    blas = None
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=cores)
+        from threadpoolctl import threadpool_info
+        blas = max((d.get("num_threads", 1) for d in threadpool_info()), default=None)
+    except Exception:
+        pass
+    return cores, torch.get_num_threads(), blas
+
+
+class CpuReference:
+    """The reference's CPU path for one configuration, as two restatements timed side by side (BASELINE.md section 2;
+    jax / numpyro are not installed, so the reference's own jit(value_and_grad(potential_fn)) cannot run):
+    (i) oracle/model.py: numpy, fp32 emulator, hand-written reverse mode, BLAS threads = all cores;
+    (ii) oracle/torch_ref.py: torch-CPU fp32 autograd value_and_grad, torch threads = all cores.
+    The stars are evaluated in chunks of <= 50 000 (memory); a step over S stars is the sum of its chunks."""
+    CHUNK = 50_000
+
+    def __init__(self, cfg, n_stars):
+        import torch
+        from oracle import model as M, synth
+        from oracle.bc import GridInterpolator, synthetic_grid
+        from oracle.nets import load_emulator
+        from oracle.torch_ref import TorchPotential
+        self.M, self.torch = M, torch
+        self.chunks = []
+        left = n_stars
+        grid = GridInterpolator(*synthetic_grid()) if cfg["phot"] else None
+        emu = load_emulator(np.float32)
+        while left > 0:
+            m = min(left, self.CHUNK)
+            if m == 1 and n_stars > 1:
+                m, left = 2, left + 1
+            spec = M.ModelSpec(cfg["level"], m, list(cfg["obs"]), bands=3 if cfg["phot"] else 0, bc=grid,
+                               bc_mode="grid" if cfg["phot"] else "none", emulator=emu)
+            prob = synth.make_problem(spec, seed=len(self.chunks))
+            tp = TorchPotential(spec, prob[1], prob[2], prob[3], prob[4], dtype=torch.float32)
+            self.chunks.append((spec, prob, tp))
+            left -= m
+        self.n = n_stars
+
+    def step(self, impl):
+        u = 0.0
+        for spec, (z0, obs, diag, ml, ms), tp in self.chunks:
+            u += tp.value_and_grad(z0)[0] if impl == "torch" else self.M.potential_and_grad(spec, z0, obs, diag, ml, ms)[0]
+        return u
+
+    def time(self, impl, steps, warmup):
+        for _ in range(warmup):
+            self.step(impl)
+        t = []
+        for _ in range(steps):
+            t0 = time.perf_counter()
+            self.step(impl)
+            t.append(time.perf_counter() - t0)
+        return t
+
+
+def cpu_reference(cfg, n_total, budget_s, steps=None, warmup=1):
+    """Times both CPU restatements on the FULL workload when `steps` + `warmup` calls of it fit into budget_s (per
+    implementation), else on the largest star sample that does (then the full-workload rate is the measured rate
+    scaled by stars, cost being linear in stars, and both are reported).  Returns the dict for `cpu_baseline`."""
+    cores, torch_threads, blas_threads = host_threads()
+    probe_n = min(n_total, 20_000)
+    probe = CpuReference(cfg, probe_n)
+    per_star = {}
+    for impl in ("torch", "numpy"):
+        probe.step(impl)
         t0 = time.perf_counter()
-        M.potential_and_grad(spec, z0, obs, diag, ml, ms)
-        times.append(time.perf_counter() - t0)
-        if steps is not None and len(times) >= steps:
-            break
-        if steps is None and (time.perf_counter() - t_start > budget_s or len(times) >= 200):
-            break
-    t = float(np.median(times))
-    cores = os.cpu_count() or 1
-    rate = 1.0 / (t * n_total / sample)
-    desc = (f"oracle port (numpy, fp32 emulator, manual reverse mode), {sample} of {n_total} stars per timed call, "
-            f"median of {len(times)} calls = {t * 1e3:.1f} ms, extrapolated linearly in stars")
-    return rate, cores, desc, t
+        probe.step(impl)
+        per_star[impl] = (time.perf_counter() - t0) / probe_n
+    calls = (steps if steps is not None else 3) + warmup
+    res = {}
+    for impl in ("torch", "numpy"):
+        fit = int(budget_s / 2 / calls / per_star[impl])
+        sample = n_total if fit >= n_total else max(min(probe_n, n_total), fit // 1000 * 1000)
+        ref = probe if sample == probe_n else CpuReference(cfg, sample)
+        k = steps if steps is not None else max(2, min(20, int(budget_s / 2 / (per_star[impl] * sample)) - warmup))
+        t = ref.time(impl, k, warmup)
+        med = float(np.median(t))
+        res[impl] = dict(sample_stars=sample, calls=len(t), ms_per_call=med * 1e3, measured_evals_per_s=1.0 / med,
+                         full_workload_evals_per_s=1.0 / (med * n_total / sample), total_s=float(np.sum(t)))
+    best = max(res, key=lambda k: res[k]["full_workload_evals_per_s"])
+    r = res[best]
+    full = r["sample_stars"] == n_total
+    names = {"torch": "oracle/torch_ref.py (torch-CPU fp32 autograd value_and_grad)",
+             "numpy": "oracle/model.py (numpy, fp32 emulator, manual reverse mode)"}
+    desc = (f"{names[best]}: {'the full workload' if full else str(r['sample_stars']) + ' of ' + str(n_total) + ' stars'} "
+            f"per timed call, median of {r['calls']} calls = {r['ms_per_call']:.1f} ms"
+            + ("" if full else ", scaled linearly in stars to the full workload"))
+    return {"value": r["full_workload_evals_per_s"], "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc,
+            "threads": {"torch": torch_threads, "blas": blas_threads, "OMP_NUM_THREADS_env": os.environ.get("OMP_NUM_THREADS")},
+            "implementation": best, "full_workload_timed": full, "measured": res,
+            "ms_per_step": 1e3 / r["full_workload_evals_per_s"]}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    rate, cores, desc, t = cpu_reference_rate(args.stars, args.cpu_sample, steps=args.steps, warmup=max(args.warmup, 1))
+    cb = cpu_reference(args.cfg, args.stars, args.ref_budget, steps=args.steps, warmup=max(args.warmup, 1))
+    rate = cb["value"]
     line = {
         "impl": "reference", "metric": "logp+grad evals/s", "value": rate, "unit": "evals/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / rate, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, "cpu"),
-        "cpu_baseline": {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc},
+        "cpu_baseline": cb,
         "e2e": {"value": rate, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference JAX-CPU unavailable on this box (jax, numpyro, h5py not installed, no network): the CPU "
-                "restatement of the same path is timed instead",
+                "restatements of the same path are timed instead, the faster one is reported",
     }
     emit(line)
 
 
 def workload_config(args, engine):
-    return {"workload": "BASELINE config 4: HierarchicalStarModel spec+phot, observables "
-                        "[log_Teff, log_g, mag(G,BP,RP), plx], kind=diag, BC table 70x26x18x13 (synthetic MIST stand-in)",
-            "stars": args.stars, "sites_per_star": 7, "hyper_sites": 5, "engine": engine,
+    cfg = args.cfg
+    hier = cfg["level"] == "hierarchical"
+    return {"workload": cfg["text"], "config": args.config,
+            "stars": args.stars, "sites_per_star": (6 if hier else 8) + (1 if cfg["phot"] else 0),
+            "hyper_sites": 5 if hier else 0, "engine": engine,
             "parallelism": f"star-sharded x{args.gpus}, one 6-double allreduce per evaluation"
                            + (" (fused into the kernel over NVLink peer memory)" if getattr(args, "fused", False) else
                               (" (NCCL)" if args.gpus > 1 else "")),
@@ -195,9 +305,17 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
-    grid = synthetic.synthetic_bc_grid(bands=3)
-    model = ssi.HierarchicalStarModel(args.stars, list(OBSERVABLES), bands=BANDS, bc="grid", bc_grid=grid,
-                                      engine=args.engine, device=local)
+    cfg = args.cfg
+    grid = synthetic.synthetic_bc_grid(bands=3) if cfg["phot"] else None
+
+    def make_model():
+        kw = dict(engine=args.engine, device=local)
+        if cfg["phot"]:
+            kw.update(bands=BANDS, bc="grid", bc_grid=grid)
+        cls = ssi.HierarchicalStarModel if cfg["level"] == "hierarchical" else ssi.MultiStarModel
+        return cls(args.stars, list(cfg["obs"]), **kw)
+
+    model = make_model()
     z0, obs, diag, ml, ms, _ = synthetic.make_problem(model, args.stars)
     model.set_shard(rank, world)
     zl, obs_l, diag_l, ml_l, ms_l = shard_problem(z0, obs, diag, ml, ms, rank, world)
@@ -268,21 +386,23 @@ def run_b200(args):
     from scalable_stellar_inference_b200.parallel import PipelinedHostPotential, ZeroCopyHostPotential
     from scalable_stellar_inference_b200.parallel import bind_host_to_device, block_bounds, shard_bounds, slice_problem
     lo_r, hi_r = shard_bounds(args.stars, rank, world)
-    prev_affinity = bind_host_to_device(local)   # pinned buffers and the launching thread next to the GPU's PCIe root
+    numa = bind_host_to_device(local)   # pinned buffers and the launching thread next to the GPU's PCIe root
+    prev_affinity = numa.get("previous")
+    numa = {k: v for k, v in numa.items() if k != "previous"}
     if args.e2e_mode == "zerocopy":
         # the device-resident model of this rank (same handle, shard and exchange) fed from host memory
         pipe = ZeroCopyHostPotential(model)
         pipe.load(model.flatten(zl))
         B, bounds = 1, [(lo_r, hi_r)]
-        e2e_api = "csi_potential_host on page-locked buffers (parallel.ZeroCopyHostPotential.value_and_grad_host)"
+        e2e_api = ("csi_potential on page-locked host buffers, K steps queued, one synchronisation "
+                   "(parallel.ZeroCopyHostPotential.enqueue / wait)")
     else:
         bounds = block_bounds(lo_r, hi_r, max(1, args.e2e_blocks), unit=2 * 128 * model.info()["sm_count"],
                               ramp=not args.e2e_equal)
         B = len(bounds)
         blocks, zb = [], []
         for b, (lo_b, hi_b) in enumerate(bounds):
-            mb = ssi.HierarchicalStarModel(args.stars, list(OBSERVABLES), bands=BANDS, bc="grid", bc_grid=grid,
-                                           engine=args.engine, device=local)
+            mb = make_model()
             mb.set_shard(rank * B + b, world * B)   # hyper-prior terms on the first block of rank 0 only
             zl_b, obs_b, diag_b, ml_b, ms_b = slice_problem(z0, obs, diag, ml, ms, lo_b, hi_b)
             mb.condition(obs_b, diag_b, M_H_loc=ml_b, M_H_scale=ms_b)
@@ -297,9 +417,23 @@ def run_b200(args):
     for k in range(K):
         u_h, gh_h, g_h = pipe.value_and_grad_host()      # synchronises the host: wall clock brackets real work
     torch.cuda.synchronize(dev)
-    e2e_ms = (time.perf_counter() - t_e2e) * 1e3
+    e2e_sync_ms = (time.perf_counter() - t_e2e) * 1e3
     barrier()
-    e2e_total = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+    e2e_ms = e2e_sync_ms
+    e2e_async = args.e2e_mode == "zerocopy" and (world == 1 or fused)
+    if e2e_async:
+        # the same K evaluations queued back to back (stream-ordered csi_potential on the pinned buffers, every step
+        # reads its sites from and writes its gradient and sums to host memory) with ONE host synchronisation at the
+        # end: how a device-side sampler drives the path -- no host-paced barrier between the ranks' steps
+        pipe.enqueue(); pipe.wait()
+        barrier()
+        t_e2e = time.perf_counter()
+        for k in range(K):
+            pipe.enqueue()
+        u_h = pipe.wait()[0]
+        e2e_ms = (time.perf_counter() - t_e2e) * 1e3
+        barrier()
+    e2e_total = torch.tensor([e2e_ms, e2e_sync_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_total, op=dist.ReduceOp.MAX)
     clocks = sampler.stop()
@@ -307,8 +441,8 @@ def run_b200(args):
         os.sched_setaffinity(0, prev_affinity)   # the CPU baseline below uses every host core again
     if not (np.isfinite(u_h) and abs(u_h - u_first) <= 1e-7 * abs(u_first)) and not os.environ.get("CSI_TC_DEBUG"):
         raise SystemExit(f"e2e result {u_h} differs from the device-resident result {u_first}")
-    if args.e2e_mode == "zerocopy" and os.environ.get("CSI_HOST_GATE_EXP", "0") == "0" \
-            and not torch.equal(pot.grad_dev.cpu()[5:], pipe.grad_pin[5:]):
+    nh_ = len(model.hyper_sites)
+    if args.e2e_mode == "zerocopy" and not torch.equal(pot.grad_dev.cpu()[nh_:], pipe.grad_pin[nh_:]):
         raise SystemExit("zero-copy gradient differs from the device-resident gradient")
 
     if rank == 0:
@@ -318,18 +452,24 @@ def run_b200(args):
         stars_local = model.n_local
         achieved = FLOP_PER_STAR * stars_local / (kern * 1e-3) / 1e12
         traffic, ncu = ncu_traffic()
-        if ncu is not None and (ncu.get("stars") != stars_local or world != 1):
-            traffic = None  # the capture is of the 1-GPU, 1 M-star launch only
+        if ncu is not None and (ncu.get("stars") != stars_local or world != 1 or args.config != "c4"):
+            traffic = None  # the capture is of the 1-GPU, 1 M-star config-4 launch only
+        n_sites_, k_obs = len(model.star_sites), len(model.observable_indices)
+        alg_bytes = (2 * n_sites_ + 2 * k_obs + 3) * 4 * stars_local   # sites in, gradients out, obs + diag, M_H prior
         line = {
             "metric": "logp+grad evals/s", "value": 1e3 / ms_per_step, "unit": "evals/s", "n_gpus": world,
             "steps": K, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (fp16 hi/lo split x3 MMA, fp32 accumulate)",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32 (fp16 hi/lo split x3 MMA, fp32 accumulate)"
+            if args.engine == "tcgen05" else "f32",
             "data": "synthetic", "config": workload_config(args, model.info()["engine"]),
             "star_evals_per_s": args.stars * 1e3 / ms_per_step,
-            "e2e": {"value": 1e3 / (float(e2e_total.item()) / K), "unit": "evals/s",
+            "e2e": {"value": 1e3 / (float(e2e_total[0].item()) / K), "unit": "evals/s",
                     "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+                    "sync_per_step": {"value": 1e3 / (float(e2e_total[1].item()) / K), "unit": "evals/s",
+                                      "api": "csi_potential_host, one host synchronisation per step"},
+                    "host_syncs_in_timed_region": 1 if e2e_async else K,
                     "blocks": B, "block_stars": [hi_b - lo_b for lo_b, hi_b in bounds],
-                    "host_bound_to_gpu_numa_node": prev_affinity is not None,
+                    "host_numa": numa,
                     "mode": args.e2e_mode, "cuda_graph": getattr(pipe, "graph", None) is not None,
                     "api": e2e_api},
             "gpu_launches": int(gpu_launches), "gpu_launches_e2e_per_step": B,
@@ -337,7 +477,10 @@ def run_b200(args):
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": bf16_peak, "unit": "TFLOP/s",
                          "frac": achieved / bf16_peak, "traffic": traffic,
                          "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full)",
-                         "algorithmic_bytes": 29 * 4 * stars_local,
+                         "traffic_source": None if traffic is None else
+                         f"committed ncu capture profiles/potential_ncu.json @ {git_sha('profiles/potential_ncu.json')} "
+                         "(a constant of that capture, not a measurement of this run)",
+                         "algorithmic_bytes": alg_bytes,
                          "kernel": "potential_tc_kernel" if args.engine == "tcgen05" else "potential_ffma_kernel",
                          "kernel_ms": kern, "stars_per_launch": stars_local, "flop_per_star": FLOP_PER_STAR,
                          "peak_source": which + "; fp16/bf16 dense tensor peak",
@@ -347,8 +490,7 @@ def run_b200(args):
             "potential": u_first,
         }
         if world == 1 and not args.no_cpu_baseline:
-            rate, cores, desc, _ = cpu_reference_rate(args.stars, args.cpu_sample, budget_s=15.0)
-            line["cpu_baseline"] = {"value": rate, "unit": "evals/s", "cores": cores, "kind": "port", "sample": desc}
+            line["cpu_baseline"] = cpu_reference(args.cfg, args.stars, args.cpu_budget)
         emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -70,32 +70,88 @@ def _parse_cpulist(text: str):
     return cpus
 
 
-def bind_host_to_device(device: int):
-    """Restrict this process to the CPU cores that share a PCIe root / NUMA node with GPU ``device`` (Linux sysfs
-    ``local_cpulist`` of the GPU's PCI function) and return the previous affinity mask, or None when the topology
-    is not visible (containers without sysfs PCI entries) -- then nothing is changed.  Pinned host buffers
-    allocated afterwards are first-touched on that node, so the H2D / D2H copies of the host-buffer path do not
-    cross the socket interconnect; without it the end-to-end rate depends on where the scheduler happened to put
-    the process.  Undo with ``os.sched_setaffinity(0, previous)``."""
-    import os
+def _gpu_pci_bus_id(device: int):
+    """PCI bus id ("0000:1b:00.0") of CUDA device ``device`` of this process, through torch (honours
+    CUDA_VISIBLE_DEVICES) or, failing that, NVML."""
     try:
-        import pynvml
-        pynvml.nvmlInit()
-        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-        index = int(vis.split(",")[device]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else device
-        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
-        bus = bus.decode() if isinstance(bus, bytes) else bus
-        dom, rest = bus.lower().split(":", 1)
-        with open(f"/sys/bus/pci/devices/{dom[-4:]}:{rest}/local_cpulist") as f:
-            local = _parse_cpulist(f.read())
+        import torch
+        p = torch.cuda.get_device_properties(device)
+        return f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+    except Exception:
+        pass
+    import os
+    import pynvml
+    pynvml.nvmlInit()
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    index = int(vis.split(",")[device]) if vis and all(t.strip().isdigit() for t in vis.split(",")) else device
+    bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+    bus = bus.decode() if isinstance(bus, bytes) else bus
+    dom, rest = bus.lower().split(":", 1)
+    return f"{dom[-4:]}:{rest}"
+
+
+def gpu_local_cpus(device: int):
+    """(cpus, how): the host cores that share a NUMA node / PCIe root with GPU ``device`` -- sysfs ``local_cpulist``
+    of the GPU's PCI function, else its ``numa_node`` -> ``/sys/devices/system/node/nodeN/cpulist``, else
+    ``nvidia-smi topo -C``'s answer; (None, reason) when the topology is not visible."""
+    import os
+    import subprocess
+    try:
+        bus = _gpu_pci_bus_id(device)
+    except Exception as e:  # noqa: BLE001
+        return None, f"no PCI bus id ({type(e).__name__})"
+    base = f"/sys/bus/pci/devices/{bus}"
+    try:
+        with open(f"{base}/local_cpulist") as f:
+            cpus = _parse_cpulist(f.read())
+        if cpus:
+            return cpus, f"sysfs local_cpulist of {bus}"
+    except OSError:
+        pass
+    try:
+        with open(f"{base}/numa_node") as f:
+            node = int(f.read().strip())
+        if node >= 0:
+            with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                return _parse_cpulist(f.read()), f"sysfs numa_node {node} of {bus}"
+    except (OSError, ValueError):
+        pass
+    try:
+        out = subprocess.run(["nvidia-smi", "topo", "-C", "-i", str(device)], capture_output=True, text=True, timeout=20).stdout
+        for line in out.splitlines():
+            if "NUMA" in line.upper() and ":" in line:
+                ids = line.split(":")[-1].strip()
+                if ids and ids[0].isdigit():
+                    node = int(ids.split(",")[0].split("-")[0])
+                    with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                        return _parse_cpulist(f.read()), f"nvidia-smi topo -C: NUMA node {node}"
+    except Exception:  # noqa: BLE001
+        pass
+    return None, f"no topology in sysfs for {bus}"
+
+
+def bind_host_to_device(device: int):
+    """Restrict this process to the CPU cores next to GPU ``device`` (see ``gpu_local_cpus``), so that the pinned host
+    buffers allocated afterwards are first-touched on that node and the launching thread runs there: the host-buffer
+    path then does not cross the socket interconnect.  Returns a dict: ``local`` = the process now runs on the
+    GPU's node (it was bound, or its affinity mask was inside the node already), ``bound`` = the mask was changed,
+    ``how`` = where the topology came from / why nothing was done, ``previous`` = the old mask when it was changed
+    (undo with ``os.sched_setaffinity(0, previous)``)."""
+    import os
+    cpus, how = gpu_local_cpus(device)
+    if cpus is None:
+        return dict(local=False, bound=False, how=how, previous=None)
+    try:
         previous = os.sched_getaffinity(0)
-        target = local & previous
-        if not target or target == previous:
-            return None
+        target = cpus & previous
+        if not target:
+            return dict(local=False, bound=False, how=how + "; none of those cores is available to this process", previous=None)
+        if target == previous:
+            return dict(local=True, bound=False, how=how + "; the process was confined to that node already", previous=None)
         os.sched_setaffinity(0, target)
-        return previous
-    except Exception:  # no NVML / sysfs / affinity support: leave the process where it is
-        return None
+        return dict(local=True, bound=True, how=how, previous=previous, cores=len(target))
+    except (AttributeError, OSError) as e:
+        return dict(local=False, bound=False, how=how + f"; sched_setaffinity: {e}", previous=None)
 
 
 def slice_problem(z: dict, obs, diag, mh_loc, mh_scale, lo: int, hi: int):
@@ -326,9 +382,28 @@ class ZeroCopyHostPotential:
         self.h2d_bytes, self.d2h_bytes = n * 4, n * 4 + 6 * 8
         self.launches = 0
         self._sum = torch.zeros(6, dtype=torch.float64, device=self.device)
+        self._out_pin = None
 
     def load(self, z_flat):
         self.z_pin.copy_(self.torch.as_tensor(np.asarray(z_flat, np.float32)))
+
+    def enqueue(self, stream=None):
+        """Queue one evaluation on ``stream`` (default: torch's current stream) and return at once: ``csi_potential``
+        on the page-locked buffers (with unified addressing a cudaHostAlloc pointer is its own device alias).  The
+        kernel reads the sites from host memory and writes the gradient and the 6 sums back to it; call ``wait()``
+        before touching them.  Needs the fused peer exchange when sharded (an NCCL allreduce of host memory would
+        need a staging copy)."""
+        torch = self.torch
+        if self._out_pin is None:
+            self._out_pin = torch.zeros(8, dtype=torch.float64).pin_memory()
+        st = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        self.model.potential_device(self.z_pin.data_ptr(), self._out_pin.data_ptr(), self.grad_pin.data_ptr(), st)
+        self.launches += 1
+
+    def wait(self, stream=None):
+        (stream or self.torch.cuda.current_stream(self.device)).synchronize()
+        tot = self._out_pin[:6].numpy().copy()
+        return float(tot[0]), tot[1:6], self.grad_view
 
     def value_and_grad_host(self):
         """Returns (U, dU/dhyper[5], grad_view); the per-star gradients are in the pinned buffer when it returns."""
