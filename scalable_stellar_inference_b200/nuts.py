@@ -131,7 +131,7 @@ class NUTS:
         if not math.isfinite(de):
             de = math.inf
         return _Tree(z1, r1, g1, z1, r1, g1, z1, u1, g1, -de, r1, False, de > self.max_de,
-                     min(1.0, math.exp(-de)) if de < math.inf else 0.0, 1)
+                     math.exp(min(-de, 0.0)) if de < math.inf else 0.0, 1)
 
     def _combine(self, cur: _Tree, new: _Tree, going_right: bool, biased: bool):
         log_w = _logaddexp(cur.log_w, new.log_w)
@@ -361,7 +361,7 @@ class IterativeNUTS:
                     de = math.inf
                 w = -de
                 div = de > self.max_de
-                sum_acc += min(1.0, math.exp(-de)) if de < math.inf else 0.0
+                sum_acc += math.exp(min(-de, 0.0)) if de < math.inf else 0.0
                 n_prop += 1
                 if leaf == 0:
                     take, logw_sub = True, w

@@ -46,7 +46,7 @@ def test_device_transitions_match_the_host_restatement(name, n, engine):
     nuts = DeviceNUTS(model, zf, seed=11, max_tree_depth=6)
     ref = IterativeNUTS(pot, seed=11, max_tree_depth=6, dtype=np.float32)
     L = zf.size
-    step = 0.5 * nuts.find_heuristic_step_size()
+    step = (0.12 if name == "hier_phot_grid" else 0.5) * nuts.find_heuristic_step_size()   # several doublings per transition
     nuts.inv_mass.copy_(torch.rand(L, device=nuts.dev) * 0.5 + 0.75)   # exercise a non-trivial mass matrix
     torch.cuda.synchronize(nuts.dev)   # the sampler runs on its own stream
     agree, depths, total = 0, [], 12
