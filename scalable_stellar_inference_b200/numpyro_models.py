@@ -65,18 +65,30 @@ def _default_const(const: Optional[dict] = None) -> dict:
     return const
 
 
-def _tn(d) -> _lib.Tn:
-    return _lib.Tn(float(np.mean(d["loc"])), float(np.mean(d["scale"])), float(d.get("low", -inf)), float(d.get("high", inf)))
+def _tn(d, name="") -> _lib.Tn:
+    """Truncated-normal constants of one site.  The reference's ``TruncatedNormal(**const[...])`` also accepts per-star
+    ARRAYS for loc / scale (scripts/model_star.py:126-128 does that for M_H); the C ABI carries per-star arrays for
+    M_H only (``condition(M_H_loc=, M_H_scale=)``), so arrays anywhere else are an error, not silently averaged."""
+    for k in ("loc", "scale"):
+        if np.ndim(d[k]) != 0 and np.size(d[k]) != 1:
+            raise ValueError(f"const[{name!r}][{k!r}] is an array: per-star prior parameters are supported for M_H only, "
+                             "through condition(M_H_loc=..., M_H_scale=...)")
+    return _lib.Tn(float(np.reshape(d["loc"], -1)[0]), float(np.reshape(d["scale"], -1)[0]), float(d.get("low", -inf)),
+                   float(d.get("high", inf)))
 
 
 def _base_config(const: Optional[dict] = None) -> _lib.Config:
     c = _default_const(dict(const) if const else None)
     cfg = _lib.Config()
-    cfg.log_evol, cfg.log_mass, cfg.m_h = _tn(c["log_evol"]), _tn(c["log_mass"]), _tn(c["M_H"])
+    cfg.log_evol, cfg.log_mass = _tn(c["log_evol"], "log_evol"), _tn(c["log_mass"], "log_mass")
+    mh = dict(c["M_H"])
+    if np.size(mh["loc"]) > 1 or np.size(mh["scale"]) > 1:   # per-star arrays travel through condition() (see there)
+        mh["loc"], mh["scale"] = float(np.mean(mh["loc"])), float(np.mean(mh["scale"]))
+    cfg.m_h = _tn(mh, "M_H")
     cfg.y_low, cfg.y_high = c["Y"]["low"], c["Y"]["high"]
     cfg.a_low, cfg.a_high = c["a_MLT"]["low"], c["a_MLT"]["high"]
     cfg.y0_loc, cfg.y0_scale = c["Y_0"]["loc"], c["Y_0"]["scale"]
-    cfg.dydz, cfg.mu_a = _tn(c["dY_dZ"]), _tn(c["mu_a"])
+    cfg.dydz, cfg.mu_a = _tn(c["dY_dZ"], "dY_dZ"), _tn(c["mu_a"], "mu_a")
     cfg.py_conc, cfg.py_rate = c["precision_Y"]["concentration"], c["precision_Y"]["rate"]
     cfg.pa_conc, cfg.pa_rate = c["precision_a"]["concentration"], c["precision_a"]["rate"]
     cfg.delta_df = float(c["delta"]["df"])
@@ -224,7 +236,16 @@ class SingleStarModel:
         dg = None
         if diag is not None:
             dg = np.ascontiguousarray(np.broadcast_to(np.asarray(diag, np.float64), obs.shape))
+        # an observable without emulator-error variance (the parallax row) needs diag > 0: Normal(mean, sqrt(0 + 0))
+        var_obs = np.concatenate([self.variance, np.zeros(len(self.output_names) - 7)])[self.observable_indices]
+        if self.kind == "diag":
+            total = var_obs[None, :] + (0.0 if dg is None else dg)
+            if np.any(np.broadcast_to(total, obs.shape) <= 0.0):
+                bad = [self.output_names[i] for i, v in zip(self.observable_indices, np.min(np.broadcast_to(total, obs.shape), axis=0)) if v <= 0]
+                raise ValueError(f"observables {bad} have zero total variance: pass diag > 0 for them")
         ml = ms = None
+        if M_H_loc is None and (np.size(self.const["M_H"]["loc"]) > 1 or np.size(self.const["M_H"]["scale"]) > 1):
+            M_H_loc, M_H_scale = self.const["M_H"]["loc"], self.const["M_H"]["scale"]   # const arrays, as the reference takes them
         if M_H_loc is not None:
             ml = np.ascontiguousarray(np.broadcast_to(np.asarray(M_H_loc, np.float64), (n,)))
             ms = np.ascontiguousarray(np.broadcast_to(np.asarray(M_H_scale, np.float64), (n,)))
@@ -232,6 +253,19 @@ class SingleStarModel:
         _lib.check(self._lib.csi_set_data(self._h, n, p(obs), p(dg), p(ml), p(ms)))
         self.n_local = n
         return self
+
+    def __call__(self, obs=None, diag=None, *, M_H_loc=None, M_H_scale=None, rng_key=0):
+        """The model callable of the reference (``numpyro_models.py:242-245,255-259,341-346``).  numpyro runs it
+        under handlers; here it has the two effects those runs have on the hot path: with ``obs`` it CONDITIONS the
+        model (what ``mcmc.run(key, obs=y, diag=diag)`` does -- afterwards ``potential_fn`` is the conditioned
+        potential) and returns the model; with ``obs=None`` it is a prior-predictive trace
+        (``handlers.trace(handlers.seed(model, key)).get_trace(obs=None)``, tests/test_numpyro_models.py:8-17): one
+        draw of every site from the priors, the deterministic outputs through the GPU forward pass, and ``y`` sampled
+        for all outputs -- returned as a dict."""
+        if obs is not None:
+            return self.condition(obs, diag, M_H_loc=M_H_loc, M_H_scale=M_H_scale)
+        from .infer import Predictive
+        return {k: (v[0] if np.ndim(v) else v) for k, v in Predictive(self, num_samples=1)(rng_key).items()}
 
     # ---- layout ---------------------------------------------------------------------------------------
     @property
@@ -296,8 +330,10 @@ class SingleStarModel:
                     smem_bytes=a[4], grid=a[5], rank=a[6], world=a[7])
 
     # ---- forward-only (Predictive) ------------------------------------------------------------------------
-    def predict(self, z: dict) -> dict:
-        """Deterministic sites and the predicted means at ``z`` (what Predictive / numpyro.deterministic expose)."""
+    def predict(self, z: dict, constrained: bool = False) -> dict:
+        """Deterministic sites and the predicted means at ``z`` (what Predictive / numpyro.deterministic expose).
+        ``constrained=True`` adds the constrained values of the remaining sampled sites (``log_evol``, the
+        precisions, the hyper-parameters and ``sigma_Y`` / ``sigma_a``), i.e. everything ``mcmc.get_samples()`` holds."""
         lib, h, n = self._lib, self._h, self.n_local
         zf = self.flatten(z)
         ptrs = []
@@ -324,6 +360,20 @@ class SingleStarModel:
             d[nm] = par[:, i]
         if self.bands:
             d["distance"] = par[:, 7]
+        if constrained:
+            c = self.const
+            sig = lambda u: 1.0 / (1.0 + np.exp(-np.asarray(u, np.float64)))  # noqa: E731
+            d["log_evol"] = np.log10(d["evol"])
+            if self.hyper_sites:
+                d["Y_0"] = np.float64(z["Y_0"])
+                d["dY_dZ"] = c["dY_dZ"]["low"] + (c["dY_dZ"]["high"] - c["dY_dZ"]["low"]) * sig(z["dY_dZ"])
+                d["mu_a"] = c["mu_a"]["low"] + (c["mu_a"]["high"] - c["mu_a"]["low"]) * sig(z["mu_a"])
+            for nm in ("precision_Y", "precision_a"):
+                if nm in z:
+                    d[nm] = np.exp(np.asarray(z[nm], np.float64))
+                    d["sigma_" + nm[-1]] = d[nm] ** -0.5
+            if self.bands:
+                d["scaled_distance"] = d["distance"] / c["max_distance"]
         return d
 
 

@@ -92,3 +92,22 @@ def test_validation_errors():
         M.ModelSpec("single", 1, ["log_Teff"], kind="none")
     with pytest.raises(ValueError):
         M.ModelSpec("single", 1, ["log_Teff"], prior="weird")
+
+
+def test_oracle_matches_jax_fixture():
+    """The pin this image cannot produce: U and dU/dz of the REAL reference (jax + numpyro, x64), written by
+    tools/gen_jax_fixtures.py on a box that has them.  Skipped while tests/golden/potential_jax.json is absent."""
+    import json
+    import os
+    import parity_util as PU
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "potential_jax.json")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/potential_jax.json not generated (needs a box with jax + numpyro): parity unpinned")
+    fx = json.load(open(path))
+    for name, case in fx["cases"].items():
+        spec, (z0, obs, diag, ml, ms) = PU.make_problem(name, case["stars"])
+        z = {k: np.asarray(v, np.float64).reshape(np.shape(z0[k])) for k, v in case["z"].items()}
+        u, g = M.potential_and_grad(spec, z, obs, diag, ml, ms)
+        assert abs(u - case["U"]) <= 1e-9 * abs(case["U"]), name
+        for k, v in case["grad"].items():
+            np.testing.assert_allclose(np.asarray(g[k]).reshape(-1), np.asarray(v).reshape(-1), rtol=1e-7, atol=1e-8, err_msg=f"{name}/{k}")
