@@ -49,6 +49,11 @@ CONFIGS = {
     "c5": dict(level="hierarchical", obs=["log_Teff", "log_L", "log_Dnu", "log_numax"], phot=False, stars=100_000,
                text="BASELINE config 5: HierarchicalStarModel with asteroseismic likelihood, observables [log_Teff, log_L, "
                     "log_Dnu, log_numax], kind=diag"),
+    # not a BASELINE configuration: the reference's only recorded hierarchical run (notebook/hierarchical-model-analysis.ipynb
+    # cell [5]: 1000 stars, 4 chains, 16000 warm-up + 2000 samples, sampling 1970 s on 4 x A100) -- tools/nuts_bench.py
+    "r1k": dict(level="hierarchical", obs=["log_Teff", "log_L", "log_Dnu"], phot=False, stars=1_000,
+                text="the reference's recorded run: HierarchicalStarModel, 1000 stars, observables [log_Teff, log_L, log_Dnu], "
+                     "kind=diag (notebook/hierarchical-model-analysis.ipynb cell [5])"),
 }
 
 

@@ -65,16 +65,33 @@ __device__ __forceinline__ void peer_allreduce(const PeerX &px, double *vals) {
 // -------------------------------------------------------------------------------------------------
 // block reduce of the 6 partial sums + single-pass grid reduce (last block finalises, fixed order)
 // -------------------------------------------------------------------------------------------------
-__device__ __noinline__ static void block_reduce_finalize(const DevModel &m, const HyperVals &hv, HyperAcc acc, double *red_smem,
-                                      double *partials, unsigned int *counter, double *out6, float *grad_hyper,
-                                      const PeerX &px) {
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = (blockDim.x + 31) >> 5;
+// per-warp partial sums of one thread's accumulators -> red_smem[warp * 6 + j] (lane 0 writes)
+__device__ __forceinline__ void warp_partials_to_smem(const HyperAcc &acc, double *red_smem) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double v[6] = {acc.lp, acc.g[0], acc.g[1], acc.g[2], acc.g[3], acc.g[4]};
 #pragma unroll
   for (int j = 0; j < 6; ++j) {
     double s = warp_sum(v[j]);
     if (lane == 0) red_smem[warp * 6 + j] = s;
   }
+}
+
+__device__ __noinline__ static void block_reduce_finalize_tail(const DevModel &m, const HyperVals &hv, int nwarp, double *red_smem,
+                                      double *partials, unsigned int *counter, double *out6, float *grad_hyper,
+                                      const PeerX &px);
+
+__device__ __forceinline__ void block_reduce_finalize(const DevModel &m, const HyperVals &hv, HyperAcc acc, double *red_smem,
+                                      double *partials, unsigned int *counter, double *out6, float *grad_hyper,
+                                      const PeerX &px) {
+  warp_partials_to_smem(acc, red_smem);
+  block_reduce_finalize_tail(m, hv, (blockDim.x + 31) >> 5, red_smem, partials, counter, out6, grad_hyper, px);
+}
+
+// red_smem[w * 6 + j], w < nwarp: the warps' partial sums (written before the call; the barrier below orders them)
+__device__ __noinline__ static void block_reduce_finalize_tail(const DevModel &m, const HyperVals &hv, int nwarp, double *red_smem,
+                                      double *partials, unsigned int *counter, double *out6, float *grad_hyper,
+                                      const PeerX &px) {
+  const int tid = threadIdx.x;
   __syncthreads();
   __shared__ bool is_last;
   if (tid == 0) {
