@@ -324,14 +324,15 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
   if (rc == CSI_OK && cfg->engine != CSI_ENGINE_TCGEN05 && cfg->engine != CSI_ENGINE_FFMA)
     rc = fail(CSI_EINVAL, "unknown engine");
   if (rc == CSI_OK && cfg->engine == CSI_ENGINE_TCGEN05) {
-    if (!tc_supported(cfg->emulator)) rc = fail(CSI_EINVAL, "tcgen05 engine needs the 5->128x6->4 emulator with biases within 64x the largest weight");
+    if (!(cfg->emulator.n_hidden == 128 && tc_supported(cfg->emulator)))
+      rc = fail(CSI_EINVAL, "tcgen05 engine needs the 5->128x6->4 emulator with biases within 64x the largest weight");
     else if (cfg->bands > 0 && cfg->bc_mode == CSI_BC_NET)
       rc = fail(CSI_EINVAL, "tcgen05 engine: BC-emulator net inside the potential is not supported yet; use "
                             "CSI_ENGINE_FFMA or the BC table");
   }
   // The tensor-core weight images are built whenever the emulator has the supported shape: the potential uses them
   // with CSI_ENGINE_TCGEN05, the emulator operator (csi_net_forward / csi_net_vjp, which = 0) with either engine.
-  if (rc == CSI_OK && tc_supported(cfg->emulator)) {
+  if (rc == CSI_OK && cfg->emulator.n_hidden == 128 && tc_supported(cfg->emulator)) {
     {
       std::vector<uint8_t> img(tc_image_bytes(cfg->emulator)), resident(tc_resident_bytes(cfg->emulator));
       std::vector<float> small(tc_small_floats(cfg->emulator));
@@ -350,6 +351,23 @@ extern "C" int csi_create(const csi_config *cfg, csi_handle **out) {
         }
         h->tc.img = di; h->tc.resident = dr; h->tc.small = ds; h->tc.n_steps = 2 * (cfg->emulator.n_layers - 2);
       }
+    }
+  }
+  // The BC emulator as an OPERATOR (csi_net_forward / csi_net_vjp, which = 1) runs on the same tensor-core kernel with
+  // zero-padded images (4 -> 64 x 6 -> 3 inside the 5 -> 128 x 6 -> 4 layout, N = 64 MMAs over the first K-half only).
+  // Inside the potential it stays on the CUDA-core engine: a second fused MLP would need its own ReLU-mask and
+  // operand space in shared memory, which the stellar emulator's weight ring fills.
+  if (rc == CSI_OK && cfg->bc_net.n_layers > 0 && tc_supported(cfg->bc_net)) {
+    std::vector<uint8_t> img(tc_image_bytes(cfg->bc_net)), resident(tc_resident_bytes(cfg->bc_net));
+    std::vector<float> small(tc_small_floats(cfg->bc_net));
+    tc_build_images(cfg->bc_net, img.data(), resident.data(), small.data(), &h->tc_bc.act_scale, &h->tc_bc.w_scale);
+    uint8_t *di, *dr; float *ds;
+    rc = dev_upload(h, img, &di);
+    if (rc == CSI_OK) rc = dev_upload(h, resident, &dr);
+    if (rc == CSI_OK) rc = dev_upload(h, small, &ds);
+    if (rc == CSI_OK) {
+      h->tc_bc.img = di; h->tc_bc.resident = dr; h->tc_bc.small = ds; h->tc_bc.n_steps = 10;
+      h->tc_bc.half_k = tc_half_k(cfg->bc_net) ? 1 : 0;
     }
   }
   if (rc == CSI_OK) {
@@ -614,12 +632,14 @@ extern "C" int csi_net_forward(csi_handle *h, int32_t which, const float *x, flo
   const NetDev *net = pick_net(h, which);
   if (!net) return fail(CSI_EINVAL, "network not loaded");
   int rc;
-  if (which == 0 && h->tc.img && n >= kNetTcMinRows) {
-    // large batches of the stellar emulator: the tcgen05 kernel in operator mode (small ones keep the CUDA-core
-    // kernel and its plain fp32 k-order accumulation, which the single-point known-answer tests pin to 5e-7)
+  const TcWeights &tcw = which == 0 ? h->tc : h->tc_bc;
+  if (tcw.img && n >= kNetTcMinRows) {
+    // large batches: the tcgen05 kernel in operator mode (small ones keep the CUDA-core kernel and its plain fp32
+    // k-order accumulation, which the single-point known-answer tests pin to 5e-7)
     Launch L;
     memset(&L, 0, sizeof(L));
-    L.tc = h->tc; L.io.n = n; L.net_x = x; L.net_y = y; L.sm_count = h->sm_count;
+    L.tc = tcw; L.io.n = n; L.net_x = x; L.net_y = y; L.sm_count = h->sm_count;
+    L.net_nin = net->n_in; L.net_nout = net->n_out;
     rc = launch_net_tc(L, false, (cudaStream_t)stream);
   } else {
     rc = launch_net_forward(*net, x, y, n, (cudaStream_t)stream);
@@ -634,10 +654,12 @@ extern "C" int csi_net_vjp(csi_handle *h, int32_t which, const float *x, const f
   const NetDev *net = pick_net(h, which);
   if (!net) return fail(CSI_EINVAL, "network not loaded");
   int rc;
-  if (which == 0 && h->tc.img && n >= kNetTcMinRows) {
+  const TcWeights &tcw = which == 0 ? h->tc : h->tc_bc;
+  if (tcw.img && n >= kNetTcMinRows) {
     Launch L;
     memset(&L, 0, sizeof(L));
-    L.tc = h->tc; L.io.n = n; L.net_x = x; L.net_gy = gy; L.net_gx = gx; L.sm_count = h->sm_count;
+    L.tc = tcw; L.io.n = n; L.net_x = x; L.net_gy = gy; L.net_gx = gx; L.sm_count = h->sm_count;
+    L.net_nin = net->n_in; L.net_nout = net->n_out;
     rc = launch_net_tc(L, true, (cudaStream_t)stream);
   } else {
     rc = launch_net_vjp(*net, x, gy, gx, n, (cudaStream_t)stream);

@@ -21,6 +21,7 @@ struct TcWeights {
   long long *trace;        // CSI_TC_DEBUG=8: clock64 trace of one CTA (csi_tc_trace); selects the TRACE instantiation
   int debug;               // 8 + (first traced iteration << 8) + (traced CTA << 16); read by the TRACE instantiation only
   float act_scale, w_scale;  // power-of-two operand scalings (see csi_tc.cu)
+  int half_k;              // hidden width <= 64 (BC emulator, zero-padded images): N = 64 MMAs over the first K-half only
 };
 
 struct Launch {           // everything a potential launch needs
@@ -35,8 +36,9 @@ struct Launch {           // everything a potential launch needs
   float *grad_hyper;      // may be null
   float *mean_out;        // predict mode only: [n][kMaxMean]
   float *params_out;      // predict mode only: [n][8]
-  const float *net_x, *net_gy;  // emulator-operator modes: x [n][5], gy [n][4]
-  float *net_y, *net_gx;        // y [n][4], gx [n][5]
+  const float *net_x, *net_gy;  // network-operator modes: x [n][net_nin], gy [n][net_nout]
+  float *net_y, *net_gx;        // y [n][net_nout], gx [n][net_nin]
+  int net_nin, net_nout;        // 5, 4 (stellar emulator) / 4, 3 (BC emulator)
   PeerX px;               // fused allreduce over peer memory (world <= 1: off)
   int sm_count;
   // Early exit (device-side NUTS, csi_nuts.cuh): when *stop != 0 the launch returns at once without touching
@@ -64,7 +66,8 @@ size_t tc_resident_bytes(const csi_net &net);
 size_t tc_small_floats(const csi_net &net);
 void tc_build_images(const csi_net &net, uint8_t *img_host, uint8_t *resident_host, float *small_host,
                      float *act_scale, float *w_scale);
-bool tc_supported(const csi_net &net);
+bool tc_supported(const csi_net &net);   // any 7-layer net up to 5 -> 128 x 6 -> 4 (narrower ones are zero-padded)
+bool tc_half_k(const csi_net &net);     // hidden width <= 64: TcWeights::half_k
 
 }  // namespace csi
 
@@ -78,7 +81,7 @@ struct csi_handle {
   csi::DevModel model{};
   csi::NetDev emu{}, bcnet{};
   csi::GridDev grid{};
-  csi::TcWeights tc{};
+  csi::TcWeights tc{}, tc_bc{};  // tensor-core operand images: stellar emulator / BC emulator (operator only)
   std::vector<void *> owned;  // device allocations released in csi_destroy
   // data
   long long n_local = 0;

@@ -34,15 +34,16 @@
 // (28.5 KB) stay resident in shared memory.
 //
 // Warp roles (640 threads, register budgets set with setmaxnreg): warps 0-3 / 4-7 own the stars of tile slot A / B
-// (priors, likelihood, gradient stores, and columns 0-63 of every 128-wide epilogue; 160 registers); warps 8-11 /
+// (priors, likelihood, gradient stores, and columns 0-63 of every 128-wide epilogue; 152 registers); warps 8-11 /
 // 12-15 assist them (columns 64-127 of the 128-wide epilogues; 64 registers), so that a stage's A operand is complete
 // after HALF an epilogue; warps 16 / 17 issue the MMAs of slot A / B (one elected lane each; warp 16 owns the TMEM
-// allocation), warps 18 / 19 stream their weights (64 registers).
+// allocation), warps 18 / 19 stream their weights (48 registers).
 #include <cuda_fp16.h>
 
 #include <cmath>
 #include <cstddef>
 #include <cstring>
+#include <vector>
 
 #include "csi_internal.h"
 #include "csi_ptx.cuh"
@@ -63,7 +64,10 @@ constexpr uint32_t kKStep16 = 512;              // 16 (N) x 16 (K) fp16
 constexpr uint32_t kLbo = 128, kSbo = 256;
 constexpr uint32_t kHalfBytes = 16384;         // one K-half (4 K-steps) of an fp16 128x128 operand image
 constexpr int kThreads = 640;  // 8 star-owning + 8 assisting epilogue warps, 2 MMA issuers, 2 weight loaders (one per tile slot)
-constexpr int kRegsMain = 160, kRegsAssist = 64, kRegsEngine = 64, kRegsLaunch = 96;  // 256 x 160 + 256 x 64 + 128 x 64 = 65536
+// setmaxnreg moves registers inside the pool the CTA was LAUNCHED with (640 x 96), not the whole register file:
+// 256 x 152 + 256 x 64 + 128 x 48 = 61440 = 640 x 96
+constexpr int kRegsMain = 152, kRegsAssist = 64, kRegsEngine = 48, kRegsLaunch = 96;
+static_assert(256 * kRegsMain + 256 * kRegsAssist + 128 * kRegsEngine <= kThreads * kRegsLaunch, "register pool of the CTA");
 constexpr uint32_t kTmemCols = 512;
 constexpr int kGridPtsMax = 512;                // BC table axes kept in shared memory when they fit
 constexpr float kActScale = 512.0f;             // 2^9: activations up to ~127 stay finite in fp16
@@ -419,7 +423,10 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     const int t = warp - 16;
     const uint32_t full = 0xffffffffu;
     const uint32_t tmem_u = __reduce_or_sync(full, tmem) + (uint32_t)t * 256u;
-    const uint32_t idesc128 = ptx::make_idesc_f16(128, 128);
+    // hidden width <= 64 (BC emulator on zero-padded images): N = 64 and only the first K-half is contracted, so the
+    // second half of A (never written: the assisting warps skip it) is never read
+    const bool hk = L.tc.half_k != 0;
+    const uint32_t idesc128 = hk ? ptx::make_idesc_f16(128, 64) : ptx::make_idesc_f16(128, 128);
     const uint32_t idesc16 = ptx::make_idesc_f16(128, 16);
     // Descriptor words: low word = address field (16-byte units) | leading-byte offset, high word = stride | version.
     // Every operand sits at a compile-time offset inside S, so ONE register (the low word of S itself) + immediates
@@ -430,14 +437,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     constexpr uint32_t oRes16 = offsetof(Smem, resident) / 16, oAc16 = offsetof(Smem, a_const) / 16;
     static_assert(offsetof(Smem, wring) % 16 == 0 && offsetof(Smem, wbias) % 16 == 0 && offsetof(Smem, resident) % 16 == 0 &&
                   offsetof(Smem, a_const) % 16 == 0, "operand images are 16-byte aligned inside S");
-    const uint32_t ring_lo = s_lo + oRing16 + (uint32_t)t * (4 * kHalfBytes / 16);
-    const uint64_t a_const_desc = ptx::desc_from_words(s_lo + oAc16, dhi);
-    const uint64_t bias_desc = ptx::desc_from_words(s_lo + oBias16 + (uint32_t)t * (kBiasBytes / 16), dhi);
-    const uint32_t r6_lo = s_lo + oRes16 + rB6 / 16, r13_lo = s_lo + oRes16 + rB13 / 16;
-    const uint64_t r6_bias_desc = ptx::desc_from_words(s_lo + oRes16 + rB6Bias / 16, dhi);
-    const uint64_t r0_desc0 = ptx::desc_from_words(s_lo + oRes16 + rB0 / 16, dhi);
-    const uint64_t r0_desc1 = ptx::desc_from_words(s_lo + oRes16 + (rB0 + kKStepBytes) / 16, dhi);
-    const uint64_t r7_desc = ptx::desc_from_words(s_lo + oRes16 + rB7 / 16, dhi);
     constexpr uint32_t kSlot16 = 2 * kHalfBytes / 16, kLoOff16 = kHalfBytes / 16, kK128 = kKStepBytes / 16, kK16 = kKStep16 / 16;
     auto wait_bar = [&](uint64_t *bar, uint32_t parity) {
       while (!__all_sync(full, ptx::mbar_try_wait(bar, parity))) {
@@ -454,6 +453,18 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 #pragma unroll 1
       for (int s = 0; s < kNStages; ++s, ++k) {
         const bool ring = ring_stage(s);
+        // the descriptor words of this stage, re-derived from s_lo behind an opaque copy: hoisted out of the loop
+        // they would be a dozen live registers in a warp that runs on kRegsEngine
+        uint32_t sl = s_lo;
+        asm volatile("" : "+r"(sl));
+        const uint32_t ring_lo = sl + oRing16 + (uint32_t)t * (4 * kHalfBytes / 16);
+        const uint64_t a_const_desc = ptx::desc_from_words(sl + oAc16, dhi);
+        const uint64_t bias_desc = ptx::desc_from_words(sl + oBias16 + (uint32_t)t * (kBiasBytes / 16), dhi);
+        const uint32_t r6_lo = sl + oRes16 + rB6 / 16, r13_lo = sl + oRes16 + rB13 / 16;
+        const uint64_t r6_bias_desc = ptx::desc_from_words(sl + oRes16 + rB6Bias / 16, dhi);
+        const uint64_t r0_desc0 = ptx::desc_from_words(sl + oRes16 + rB0 / 16, dhi);
+        const uint64_t r0_desc1 = ptx::desc_from_words(sl + oRes16 + (rB0 + kKStepBytes) / 16, dhi);
+        const uint64_t r7_desc = ptx::desc_from_words(sl + oRes16 + rB7 / 16, dhi);
         const uint32_t d_t = tmem_u + (k & 1u) * 128u;             // D of this stage
         const uint32_t a_reg = tmem_u + ((k & 1u) ^ 1u) * 128u;    // A: in place in the previous stage's D region
         wait_bar(&S.a_ready[t][0], apar0);
@@ -489,9 +500,11 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
           if (ring) wait_bar(&S.w_full[t][1], q & 1u);
           if (ptx::elect_one()) {
             if (ring) {
-              issue_half<1, kK128>(d_t, a_reg, ring_lo + kSlot16, ring_lo + kSlot16 + kLoOff16, dhi, idesc128, false,
-                                   a_const_desc, bias_desc);
+              if (!hk)
+                issue_half<1, kK128>(d_t, a_reg, ring_lo + kSlot16, ring_lo + kSlot16 + kLoOff16, dhi, idesc128, false,
+                                     a_const_desc, bias_desc);
               ptx::mma_commit(&S.w_empty[t][1]);
+            } else if (hk) {
             } else if (s == 6) {
               issue_half<1, kK16>(d_t, a_reg, r6_lo + 4 * kK16, r6_lo + 12 * kK16, dhi, idesc16, false, a_const_desc, r6_bias_desc);
             } else {
@@ -534,7 +547,9 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         ptx::mbar_wait(&S.d_ready[t], (uint32_t)(it & 1));
         ptx::tc_fence_after();
         const uint32_t d_base = t_base + (uint32_t)((it & 1) * 128);
-        if (s <= 5) {
+        if (L.tc.half_k) {  // 64-wide network: columns 64..127 do not exist; keep the barrier protocol only
+          if (s <= 5 || (s >= 7 && s <= 12)) publish_a(1);
+        } else if (s <= 5) {
           uint32_t *mk = mask + s * 4 * 256;
           for_chunk_pair<false>(d_base, 2, [&](const uint32_t (&r)[32], int c) {
             mk[c * 256] = sign_word(r);
@@ -629,7 +644,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       float x[5];
       if (valid && NET) {
 #pragma unroll
-        for (int k = 0; k < 5; ++k) x[k] = (L.net_x[i * 5 + k] - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
+        for (int k = 0; k < 5; ++k)
+          x[k] = ((k < L.net_nin ? L.net_x[i * L.net_nin + k] : 0.0f) - sm[oInLoc + k]) * (sm[oInInv + k] * kActScale);
       } else if (valid) {
         tr.rec(501);
         StarIn in;
@@ -701,10 +717,12 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             float *mo = PREDICT ? mean_local : nullptr;
             if (NET) {
               if (MODE == M_NET_FWD) {
-                *reinterpret_cast<float4 *>(L.net_y + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                  if (c < L.net_nout) L.net_y[i * L.net_nout + c] = o[c];
               } else {
-                const float4 gq = *reinterpret_cast<const float4 *>(L.net_gy + i * 4);
-                g_o[0] = gq.x; g_o[1] = gq.y; g_o[2] = gq.z; g_o[3] = gq.w;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) g_o[c] = c < L.net_nout ? L.net_gy[i * L.net_nout + c] : 0.0f;
               }
             } else {
             StarObs so;
@@ -758,7 +776,7 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
           const int h = 12 - s;
           {  // row maximum of this stage's A operand: the owner's and the assistant's halves of the previous epilogue
             const int xo = 2 * ((s - 1) & 1) * kStageStride;
-            amax = fmaxf(xcol[xo], xcol[xo + kStageStride]);
+            amax = L.tc.half_k ? xcol[xo] : fmaxf(xcol[xo], xcol[xo + kStageStride]);  // (64-wide network: no assistant half)
           }
           const float f = pow2_scale(amax * sm[oGain + (s - 7)]) * 32.0f;  // f * |D| < 2^15
           float mx = 0.0f;
@@ -783,7 +801,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             for (int k = 0; k < 5; ++k) g_x[k] = __uint_as_float(r8[k]) * un * sm[oInInv + k];
             if (NET) {
 #pragma unroll
-              for (int k = 0; k < 5; ++k) L.net_gx[i * 5 + k] = g_x[k];
+              for (int k = 0; k < 5; ++k)
+                if (k < L.net_nin) L.net_gx[i * L.net_nin + k] = g_x[k];
             } else {
               star_post(m, io, i, st, g_x);
               acc.lp += (double)st.lp;
@@ -858,18 +877,53 @@ static void tc_scales(const csi_net &net, float *w_scale, float *bias_a) {
   *bias_a = ca;
 }
 
-bool tc_supported(const csi_net &net) {
-  if (!(net.n_layers == 7 && net.n_in == 5 && net.n_hidden == 128 && net.n_out == 4)) return false;
+// A network narrower than the kernel's 5 -> 128 x 6 -> 4 shape (the BC emulator: 4 -> 64 x 6 -> 3) runs on the same
+// operand layout zero-padded: absent inputs get weight 0 (and loc 0 / scale 1), absent hidden units weight 0 and bias
+// 0 (ReLU(0) = 0 contributes nothing, its cotangent is multiplied by zero weights), absent outputs weight 0.
+struct PaddedNet {
+  std::vector<float> w[7], b[7];
+  double in_loc[5], in_scale[5], out_loc[4], out_scale[4];
+  csi_net net{};
+};
+static bool pad_net(const csi_net &src, PaddedNet &p) {
+  if (!(src.n_layers == 7 && src.n_in >= 1 && src.n_in <= 5 && src.n_hidden >= 8 && src.n_hidden <= tc::kHid &&
+        src.n_out >= 1 && src.n_out <= 4))
+    return false;
+  for (int l = 0; l < 7; ++l) {
+    const int K = l == 0 ? 5 : tc::kHid, N = l == 6 ? 4 : tc::kHid;
+    const int k0 = l == 0 ? src.n_in : src.n_hidden, n0 = l == 6 ? src.n_out : src.n_hidden;
+    p.w[l].assign((size_t)K * N, 0.0f);
+    p.b[l].assign(N, 0.0f);
+    for (int k = 0; k < k0; ++k)
+      for (int j = 0; j < n0; ++j) p.w[l][(size_t)k * N + j] = src.weights[l][(size_t)k * n0 + j];
+    for (int j = 0; j < n0; ++j) p.b[l][j] = src.bias[l][j];
+    p.net.weights[l] = p.w[l].data();
+    p.net.bias[l] = p.b[l].data();
+  }
+  for (int k = 0; k < 5; ++k) { p.in_loc[k] = k < src.n_in ? src.in_loc[k] : 0.0; p.in_scale[k] = k < src.n_in ? src.in_scale[k] : 1.0; }
+  for (int j = 0; j < 4; ++j) { p.out_loc[j] = j < src.n_out ? src.out_loc[j] : 0.0; p.out_scale[j] = j < src.n_out ? src.out_scale[j] : 1.0; }
+  p.net.n_layers = 7; p.net.n_in = 5; p.net.n_hidden = tc::kHid; p.net.n_out = 4;
+  p.net.in_loc = p.in_loc; p.net.in_scale = p.in_scale; p.net.out_loc = p.out_loc; p.net.out_scale = p.out_scale;
+  return true;
+}
+
+bool tc_supported(const csi_net &src) {
+  PaddedNet p;
+  if (!pad_net(src, p)) return false;
   float s, ca;
-  tc_scales(net, &s, &ca);
+  tc_scales(p.net, &s, &ca);
   return std::isfinite(s) && ca <= 32768.0f;  // the bias tile must fit the fp16 range
 }
+bool tc_half_k(const csi_net &net) { return net.n_hidden <= 64; }
 size_t tc_image_bytes(const csi_net &) { return (size_t)tc::kRingImages * tc::kStepBytes; }
 size_t tc_resident_bytes(const csi_net &) { return tc::kResidentBytes; }
 size_t tc_small_floats(const csi_net &) { return tc::kSmallFloats; }
 
-void tc_build_images(const csi_net &net, uint8_t *img, uint8_t *res, float *small, float *act_scale, float *w_scale) {
+void tc_build_images(const csi_net &src, uint8_t *img, uint8_t *res, float *small, float *act_scale, float *w_scale) {
   using namespace tc;
+  PaddedNet padded;
+  pad_net(src, padded);
+  const csi_net &net = padded.net;
   float s, ca;
   tc_scales(net, &s, &ca);
   *w_scale = s;

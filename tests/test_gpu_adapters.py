@@ -30,12 +30,13 @@ def test_torch_potential_function_gradients():
     nh = len(model.hyper_sites)
     g = np.array(grad, np.float64)
     g[:nh] = out[1:1 + nh]
-    assert float(u) == out[0]
-    np.testing.assert_allclose(zf.grad.cpu().numpy(), 2.0 * g.astype(np.float32) + 1.0, rtol=2e-6, atol=1e-6)
+    assert float(u.detach()) == pytest.approx(out[0], rel=1e-12)
+    np.testing.assert_allclose(zf.grad.cpu().numpy(), 2.0 * g.astype(np.float32) + 1.0, rtol=1e-5, atol=1e-5)
     # dict interface, as numpyro's potential_fn takes it, against the oracle
     zd = {k: torch.tensor(np.asarray(v, np.float32), device="cuda", requires_grad=True) for k, v in z0.items()}
     u2 = potential_fn(model)(zd)
     u2.backward()
+    assert float(u2.detach()) == pytest.approx(out[0], rel=1e-12)
     u_ref, g_ref = M.potential_and_grad(spec, z0, obs, diag, ml, ms)
     gd = {k: v.grad.cpu().numpy().astype(np.float64).reshape(np.shape(g_ref[k])) for k, v in zd.items()}
     PU.check_parity(name, n, float(u2), gd, u_ref, g_ref, problem, spec.hyper_sites(), spec.star_sites())
@@ -59,7 +60,7 @@ def test_torch_emulator_function_input_vjp():
         (y * torch.tensor(w, device="cuda")).sum().backward()
         y_ref, masks = ref.forward(x.astype(np.float64), cache=True)
         gx_ref = ref.vjp(masks, w.astype(np.float64))
-        np.testing.assert_allclose(y.detach().cpu().numpy(), y_ref, rtol=0, atol=5e-6)
+        np.testing.assert_allclose(y.detach().cpu().numpy(), y_ref, rtol=0, atol=1e-5)   # log_age ~ 10: 1 ulp = 1e-6
         gx = xt.grad.cpu().numpy()
         assert np.linalg.norm(gx - gx_ref) / np.linalg.norm(gx_ref) < 2e-3
         r = np.abs(gx - gx_ref) / (np.abs(gx_ref) + np.sqrt(np.mean(gx_ref ** 2)))

@@ -150,3 +150,25 @@ def test_errors_mirror_reference(ssi):
     m = ssi.HierarchicalStarModel(10, ["log_Teff"])
     with pytest.raises(Exception):
         m.potential_and_grad_flat(np.zeros(3, np.float32))   # before condition()
+
+
+def test_bc_net_on_the_tensor_cores(ssi):
+    """Batches >= 2048 rows of the BC emulator (4 -> 64 x 6 -> 3) run on the tcgen05 kernel with zero-padded operand
+    images (N = 64 MMAs over the first K-half): same answers as the oracle net and as the CUDA-core path (< 2048 rows),
+    forward and input-VJP (src/celestify/_jax/bolometric_corrections.py:17-25)."""
+    bc = ssi.BolometricCorrections(["G", "BP", "RP"], "cuda")
+    rng = np.random.default_rng(8)
+    n = 9001   # not a multiple of the 128-row tile
+    x = np.stack([rng.uniform(3.45, 4.3, n), rng.uniform(2.2, 5.8, n), rng.uniform(-0.95, 0.45, n),
+                  rng.uniform(0, 3.5, n)], -1).astype(np.float32)
+    ref = load_bc_net(np.float64)
+    y_ref, masks = ref.forward(x.astype(np.float64), cache=True)
+    y = bc(x)
+    np.testing.assert_allclose(y, y_ref, rtol=0, atol=5e-6)
+    np.testing.assert_allclose(y[:1500], bc(x[:1500]), rtol=0, atol=3e-6)          # tcgen05 vs CUDA-core operator
+    g = rng.standard_normal((n, 3)).astype(np.float32)
+    gx_ref = ref.vjp(masks, g.astype(np.float64))
+    gx = bc.model_vjp(x, g)
+    assert np.linalg.norm(gx - gx_ref) / np.linalg.norm(gx_ref) < 2e-3
+    r = np.abs(gx - gx_ref) / (np.abs(gx_ref) + np.sqrt(np.mean(gx_ref ** 2)))
+    assert np.quantile(r, 0.99) < 1e-4

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Roofline numbers of the standalone operator kernels (plug point 1): BC table interpolation and its
-VJP (HBM-bound), emulator / BC-net forward and VJP (FP32 pipe).  CUDA events on the launching
+VJP (HBM-bound), emulator / BC-net forward and VJP (tensor pipe above 2048 rows).  CUDA events on the launching
 stream, inputs larger than L2, 3 warm-ups, mean of 10."""
 import ctypes as C, json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -18,6 +18,8 @@ rng = np.random.default_rng(0)
 pts = grid[0]
 xg = np.stack([rng.uniform(p[1], p[-2], n) for p in pts], 1).astype(np.float32)
 x4 = torch.from_numpy(xg).to(dev)
+x4n = torch.from_numpy(np.stack([rng.uniform(3.45, 4.3, n), rng.uniform(2.2, 5.8, n), rng.uniform(-0.95, 0.45, n),
+                                 rng.uniform(0, 3.5, n)], 1).astype(np.float32)).to(dev)   # BC emulator inputs: [log_Teff, log_g, M_H, Av]
 gy3 = torch.randn(n, 3, device=dev)
 y3 = torch.empty(n, 3, device=dev)
 gx4 = torch.empty(n, 4, device=dev)
@@ -49,7 +51,7 @@ add("csi_grid_forward (4-D table, 3 bands)", timeit(lambda: lib.csi_grid_forward
 add("csi_grid_vjp", timeit(lambda: lib.csi_grid_vjp(h, p(x4), p(gy3), p(gx4), n, C.c_void_p(st))), 16 + 12 + 16, 300)
 add("csi_net_forward (emulator 5-128x6-4)", timeit(lambda: lib.csi_net_forward(h, 0, p(x5), p(y4), n, C.c_void_p(st))), 20 + 16, 166144)
 add("csi_net_vjp (emulator)", timeit(lambda: lib.csi_net_vjp(h, 0, p(x5), p(gy4), p(gx5), n, C.c_void_p(st))), 20 + 16 + 20, 332288)
-add("csi_net_forward (BC net 4-64x6-3)", timeit(lambda: lib.csi_net_forward(h, 1, p(x4), p(y3), n, C.c_void_p(st))), 16 + 12, 41856)
-add("csi_net_vjp (BC net)", timeit(lambda: lib.csi_net_vjp(h, 1, p(x4), p(gy3), p(gx4), n, C.c_void_p(st))), 16 + 12 + 16, 83712)
+add("csi_net_forward (BC net 4-64x6-3)", timeit(lambda: lib.csi_net_forward(h, 1, p(x4n), p(y3), n, C.c_void_p(st))), 16 + 12, 41856)
+add("csi_net_vjp (BC net)", timeit(lambda: lib.csi_net_vjp(h, 1, p(x4n), p(gy3), p(gx4), n, C.c_void_p(st))), 16 + 12 + 16, 83712)
 for r in rows:
     print(json.dumps(r))
