@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Writes tests/golden/posterior_hier256.json: posterior summary of a hierarchical model under the fp64 ORACLE
+"""Writes tests/golden/posterior_hier64_seis.json: posterior summary of a hierarchical model under the fp64 ORACLE
 potential (oracle.model.potential_and_grad), sampled on the CPU with the host-recursive NUTS (nuts.NUTS, numpyro's
 settings: target 0.8, diagonal mass matrix, max depth 10).  tests/test_gpu_nuts.py compares the device-side sampler
 over the CUDA potential against it (north_star's posterior criterion).  Chains run as separate processes:
@@ -60,7 +60,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=500)
     ap.add_argument("--samples", type=int, default=400)
     ap.add_argument("--chains", type=int, default=4)
-    ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden", "posterior_hier256.json"))
+    ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden", "posterior_hier64_seis.json"))
     a = ap.parse_args()
     from scalable_stellar_inference_b200.nuts import effective_sample_size, split_rhat
     with ProcessPoolExecutor(a.chains) as ex:
