@@ -60,16 +60,6 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
                : "memory");
 }
 
-// ---- per-warpgroup register budget (all 4 warps of an aligned warpgroup execute the same instruction) ----------
-template <uint32_t kRegs>
-__device__ __forceinline__ void setmaxnreg_inc() {
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs));
-}
-template <uint32_t kRegs>
-__device__ __forceinline__ void setmaxnreg_dec() {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs));
-}
-
 __device__ __forceinline__ void prefetch_l1(const void *p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 // 4-byte asynchronous global -> shared copy (LDGSTS): no register holds the value in flight; the issuing thread sees

@@ -33,15 +33,11 @@
 // so that the MMAs of one tile overlap the epilogue of the other.  The images of the four narrow stages
 // (28.5 KB) stay resident in shared memory.
 //
-// Warp roles (640 threads, register budgets set with setmaxnreg): warps 0-3 / 4-7 own the stars of tile slot A / B
-// (priors, likelihood, gradient stores, and columns 0-63 of every 128-wide epilogue; 152 registers); warps 8-11 /
-// 12-15 assist them (columns 64-127 of the 128-wide epilogues; 64 registers), so that a stage's A operand is complete
-// after HALF an epilogue; warps 16 / 17 issue the MMAs of slot A / B (one elected lane each; warp 16 owns the TMEM
-// allocation), warps 18 / 19 stream their weights (48 registers).
+// Warp roles (320 threads): warps 0-3 epilogue of tile A, warps 4-7 epilogue of tile B, warp 8 MMA issuer
+// (one elected lane) + TMEM allocator, warp 9 weight loader.
 #include <cuda_fp16.h>
 
 #include <cmath>
-#include <cstddef>
 #include <cstring>
 #include <vector>
 
@@ -63,15 +59,10 @@ constexpr uint32_t kKStepBytes = 4096;          // 128 (N) x 16 (K) fp16
 constexpr uint32_t kKStep16 = 512;              // 16 (N) x 16 (K) fp16
 constexpr uint32_t kLbo = 128, kSbo = 256;
 constexpr uint32_t kHalfBytes = 16384;         // one K-half (4 K-steps) of an fp16 128x128 operand image
-constexpr int kThreads = 640;  // 8 star-owning + 8 assisting epilogue warps, 2 MMA issuers, 2 weight loaders (one per tile slot)
-// setmaxnreg moves registers inside the pool the CTA was LAUNCHED with (640 x 96), not the whole register file:
-// 256 x 152 + 256 x 64 + 128 x 48 = 61440 = 640 x 96
-constexpr int kRegsMain = 152, kRegsAssist = 64, kRegsEngine = 48, kRegsLaunch = 96;
-static_assert(256 * kRegsMain + 256 * kRegsAssist + 128 * kRegsEngine <= kThreads * kRegsLaunch, "register pool of the CTA");
+constexpr int kThreads = 384;  // 8 epilogue warps, 2 MMA issuers (one per tile), 2 weight loaders (one per tile)
 constexpr uint32_t kTmemCols = 512;
 constexpr int kGridPtsMax = 512;                // BC table axes kept in shared memory when they fit
 constexpr float kActScale = 512.0f;             // 2^9: activations up to ~127 stay finite in fp16
-constexpr int kXchRow = 12;  // staging rows 12..15: [stage parity][star-owning thread, assisting thread] row maxima
 
 // resident images (bytes into the resident blob)
 constexpr uint32_t rB0 = 0;                     // layer 0:  N = 128, K = 32
@@ -97,10 +88,8 @@ struct __align__(128) Smem {
   uint8_t resident[kResidentBytes];
   uint8_t a_const[kBiasBytes];   // constant A tile of the bias MMA: columns k = 0..2 hold oBiasA, rest 0
   float small[kSmallFloats];
-  uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][tile slot * 128 + row]
-  // per-star input staging column (star_take_z / star_take_obs), indexed [row][tile slot * 128 + row of the tile];
-  // during the backward stages its rows kXchRow.. carry the row maxima the two threads of a row exchange
-  float stage[kStageRows][kStageStride];
+  uint32_t mask[24][256];        // ReLU sign words: [hidden layer * 4 + chunk][epilogue thread]
+  float stage[kStageRows][kStageStride];  // per-thread input staging column (star_take_z / star_take_obs)
   StageList sites_list, obs_list;         // which arrays go into the column (built once, uniform copy loops)
   float grid_pts[kGridPtsMax];   // BC table axes + their lookup tables (copied once; the search then stays on-chip)
   unsigned short grid_lut[4][kLutBins];
@@ -164,62 +153,40 @@ __device__ __forceinline__ uint32_t sign_word(const uint32_t (&r)[32]) {
   return bits;
 }
 
-// forward chunk: D (scaled pre-activations) -> ReLU -> activation scale -> (hi, lo) -> A operand columns.
-// In place over the D chunk just consumed: columns [32c, 32c+16) = hi halves, [32c+16, 32c+32) = lo halves.
-// W = columns per tcgen05.st: 16 (one store per half-chunk of pairs) or 8 (half the live registers: the assisting
-// warps run on a 64-register budget).
-template <int W = 16>
+// forward chunk: D (scaled pre-activations) -> ReLU -> activation scale -> (hi, lo) -> A operand columns
 __device__ __forceinline__ void fwd_chunk(const uint32_t (&r)[32], float scale, uint32_t a_base, int c) {
+  uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int part = 0; part < 16 / W; ++part) {
-    uint32_t hi[W], lo[W];
-#pragma unroll
-    for (int q = 0; q < W; ++q) {
-      float v0 = fmaxf(__uint_as_float(r[2 * (part * W + q)]), 0.0f);
-      float v1 = fmaxf(__uint_as_float(r[2 * (part * W + q) + 1]), 0.0f);
-      mul2(v0, v1, scale);
-      split2(v0, v1, hi[q], lo[q]);
-    }
-    if constexpr (W == 16) {
-      ptx::tmem_st16(a_base + 32 * c, hi);
-      ptx::tmem_st16(a_base + 32 * c + 16, lo);
-    } else {
-      ptx::tmem_st8(a_base + 32 * c + W * part, hi);
-      ptx::tmem_st8(a_base + 32 * c + 16 + W * part, lo);
-    }
+  for (int q = 0; q < 16; ++q) {
+    float v0 = fmaxf(__uint_as_float(r[2 * q]), 0.0f);
+    float v1 = fmaxf(__uint_as_float(r[2 * q + 1]), 0.0f);
+    mul2(v0, v1, scale);
+    split2(v0, v1, hi[q], lo[q]);
   }
+  ptx::tmem_st16(a_base + 32 * c, hi);       // in place over the D chunk just consumed:
+  ptx::tmem_st16(a_base + 32 * c + 16, lo);  // columns [32c, 32c+16) = hi halves, [32c+16, 32c+32) = lo halves
 }
 
 // VJP chunk: D (cotangent before the ReLU mask) -> row scale -> (hi, lo) -> mask on the packed pairs -> A operand
-template <int W = 16>
 __device__ __forceinline__ void bwd_chunk(const uint32_t (&r)[32], float f, uint32_t signs, uint32_t a_base, int c) {
+  uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int part = 0; part < 16 / W; ++part) {
-    uint32_t hi[W], lo[W];
-#pragma unroll
-    for (int j = 0; j < W / 2; ++j) {
-      const int s = part * (W / 2) + j;
-      const uint32_t w = signs << s;
-      const uint32_t ma = prmt_sign<0xAABBu>(w);  // elements 4s (low half), 4s+1 (high half)
-      const uint32_t mb = prmt_sign<0x8899u>(w);  // elements 4s+2, 4s+3
-      uint32_t h0, l0, h1, l1;
-      float a0 = __uint_as_float(r[4 * s]), a1 = __uint_as_float(r[4 * s + 1]);
-      float a2 = __uint_as_float(r[4 * s + 2]), a3 = __uint_as_float(r[4 * s + 3]);
-      mul2(a0, a1, f);
-      mul2(a2, a3, f);
-      split2(a0, a1, h0, l0);
-      split2(a2, a3, h1, l1);
-      hi[2 * j] = h0 & ~ma; lo[2 * j] = l0 & ~ma;
-      hi[2 * j + 1] = h1 & ~mb; lo[2 * j + 1] = l1 & ~mb;
-    }
-    if constexpr (W == 16) {
-      ptx::tmem_st16(a_base + 32 * c, hi);
-      ptx::tmem_st16(a_base + 32 * c + 16, lo);
-    } else {
-      ptx::tmem_st8(a_base + 32 * c + W * part, hi);
-      ptx::tmem_st8(a_base + 32 * c + 16 + W * part, lo);
-    }
+  for (int s = 0; s < 8; ++s) {
+    const uint32_t w = signs << s;
+    const uint32_t ma = prmt_sign<0xAABBu>(w);  // elements 4s (low half), 4s+1 (high half)
+    const uint32_t mb = prmt_sign<0x8899u>(w);  // elements 4s+2, 4s+3
+    uint32_t h0, l0, h1, l1;
+    float a0 = __uint_as_float(r[4 * s]), a1 = __uint_as_float(r[4 * s + 1]);
+    float a2 = __uint_as_float(r[4 * s + 2]), a3 = __uint_as_float(r[4 * s + 3]);
+    mul2(a0, a1, f);
+    mul2(a2, a3, f);
+    split2(a0, a1, h0, l0);
+    split2(a2, a3, h1, l1);
+    hi[2 * s] = h0 & ~ma; lo[2 * s] = l0 & ~ma;
+    hi[2 * s + 1] = h1 & ~mb; lo[2 * s + 1] = l1 & ~mb;
   }
+  ptx::tmem_st16(a_base + 32 * c, hi);       // in place over the D chunk just consumed:
+  ptx::tmem_st16(a_base + 32 * c + 16, lo);  // columns [32c, 32c+16) = hi halves, [32c+16, 32c+32) = lo halves
 }
 
 // power of two f with f * x in [2^9, 2^10) (1 when x is 0 / non-finite)
@@ -236,27 +203,22 @@ __device__ __forceinline__ float pow2_scale(float x) {
 // pack two fp16 bit patterns (low, high)
 __device__ __forceinline__ uint32_t pack16(uint32_t lo16, uint32_t hi16) { return (lo16 & 0xffffu) | (hi16 << 16); }
 
-// Two adjacent 32-column chunks (c0, c0 + 1) of a D region = one K-half of the next stage's A operand.  f(r, c)
-// consumes chunk c and may overwrite ITS columns (the A operand is written in place).  DOUBLE: the tcgen05.ld of the
-// second chunk is in flight while the first is processed (two register sets); otherwise one set, one chunk at a time.
-template <bool DOUBLE, class F>
-__device__ __forceinline__ void for_chunk_pair(uint32_t d_base, int c0, F &&f) {
-  if constexpr (DOUBLE) {
-    uint32_t r0[32], r1[32];
-    ptx::tmem_ld32(d_base + 32 * c0, r0);
-    ptx::tmem_wait_ld_dep(r0);
-    ptx::tmem_ld32(d_base + 32 * c0 + 32, r1);
-    f(r0, c0);
-    ptx::tmem_wait_ld_dep(r1);
-    f(r1, c0 + 1);
-  } else {
-    uint32_t r[32];
+// D chunks (4 x 32 columns) through a two-register-set pipeline: the tcgen05.ld of the next chunk is in flight
+// while the current one is processed.  f(r, c) consumes chunk c (and may overwrite ITS columns: the A operand of
+// the next stage is written in place, chunk by chunk).
+template <class F>
+__device__ __forceinline__ void for_chunks(uint32_t d_base, int ncc, F &&f) {
+  uint32_t r0[32], r1[32];
+  ptx::tmem_ld32(d_base, r0);
+  ptx::tmem_wait_ld_dep(r0);
 #pragma unroll 1
-    for (int c = c0; c < c0 + 2; ++c) {
-      ptx::tmem_ld32(d_base + 32 * c, r);
-      ptx::tmem_wait_ld_dep(r);
-      f(r, c);
-    }
+  for (int cc = 0; cc < ncc; ++cc) {
+    ptx::tmem_ld32(d_base + 64 * cc + 32, r1);
+    f(r0, 2 * cc);
+    ptx::tmem_wait_ld_dep(r1);
+    if (cc + 1 < ncc) ptx::tmem_ld32(d_base + 64, r0);
+    f(r1, 2 * cc + 1);
+    if (cc + 1 < ncc) ptx::tmem_wait_ld_dep(r0);
   }
 }
 
@@ -339,8 +301,8 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     if (L.tc.trace && (int)blockIdx.x == (L.tc.debug >> 16) && tid == 0) ctr.p = L.tc.trace + 5 * 1024;
   ctr.rec(1);
   // ---- one-time setup ----------------------------------------------------------------------------
-  // The last warp initialises the barriers and evaluates the hyper-parameter terms (a ~3 k-cycle dependent chain
-  // behind a cold global load) while the other warps copy the resident operands, so the two run side by side.
+  // Warp 11 initialises the barriers and evaluates the hyper-parameter terms (a ~3 k-cycle dependent chain behind
+  // a cold global load) while warps 0..10 copy the resident operands, so the two run side by side.
   constexpr int kCopyThreads = kThreads - 32;
   GridDev gl = L.grid;
   const bool grid_in_smem = BC == 1 && gl.shape[0] + gl.shape[1] + gl.shape[2] + gl.shape[3] <= kGridPtsMax;
@@ -380,24 +342,31 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     if (m.prior_mode == P_HIER) hyper_eval(m, io.z_hyper, h);
     S.hv = h;
   }
+  if (grid_in_smem) {
+    int off = 0;
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      gl.pts[d] = S.grid_pts + off;
+      gl.lut[d] = S.grid_lut[d];
+      off += gl.shape[d];
+    }
+  }
   ptx::fence_proxy_async_smem();  // generic-proxy writes above are read by tcgen05.mma (async proxy)
-  if (warp == 16) ptx::tmem_alloc<kTmemCols>(&S.tmem_base);
+  if (warp == 8) ptx::tmem_alloc<kTmemCols>(&S.tmem_base);
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = S.tmem_base;
+  const HyperVals hv = S.hv;
+  HyperAcc acc{};
   ctr.rec(2);
-  // register budgets per role (the kernel is launched with kRegsLaunch per thread; the sum below is the whole file)
-  if (warp >= 16) ptx::setmaxnreg_dec<kRegsEngine>();
-  else if (warp >= 8) ptx::setmaxnreg_dec<kRegsAssist>();
-  else ptx::setmaxnreg_inc<kRegsMain>();
 
-  if (warp >= 18) {
-    // ===== weight loaders: warp 18 + t streams the images of tile slot t, one K-half per slot =============
+  if (warp >= 10) {
+    // ===== weight loaders: warp 10 + t streams the images of tile slot t, one K-half per slot =============
     // The two tiles of a CTA run out of phase (see the start gate below), so each has its own stream: slot h of
     // tile t holds K-steps 4h..4h+3 of the (hi, lo) images of the tile's current 128 x 128 stage and is refilled
     // with the next stage's half as soon as the MMAs that read it have completed (tcgen05.commit -> w_empty).
-    const int t = warp - 18;
+    const int t = warp - 10;
     if (lane == 0) {
       const long long total = slot_iters(t) * kNRing * 2;
       for (long long it = 0; it < total; ++it) {
@@ -415,28 +384,31 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
       }
     }
     __syncwarp();
-  } else if (warp >= 16) {
-    // ===== MMA issuers: warp 16 + t issues the tensor work of tile slot t ================================
+  } else if (warp >= 8) {
+    // ===== MMA issuers: warp 8 + t issues the tensor work of tile slot t =================================
     // Everything here is kept PROVABLY warp-uniform (barrier tests through a vote, the TMEM base through a warp
     // reduction, all addresses derived from parameters, constants and loop counters): ptxas then holds the
     // tcgen05.mma operands in uniform registers instead of wrapping every UTCHMMA in an elect / R2UR / branch loop.
-    const int t = warp - 16;
+    const int t = warp - 8;
     const uint32_t full = 0xffffffffu;
     const uint32_t tmem_u = __reduce_or_sync(full, tmem) + (uint32_t)t * 256u;
     // hidden width <= 64 (BC emulator on zero-padded images): N = 64 and only the first K-half is contracted, so the
-    // second half of A (never written: the assisting warps skip it) is never read
-    const bool hk = L.tc.half_k != 0;
+    // second half of A (never written: the epilogue converts chunks 0, 1 only) is never read
+    const bool hk = NET && L.tc.half_k != 0;
     const uint32_t idesc128 = hk ? ptx::make_idesc_f16(128, 64) : ptx::make_idesc_f16(128, 128);
     const uint32_t idesc16 = ptx::make_idesc_f16(128, 16);
-    // Descriptor words: low word = address field (16-byte units) | leading-byte offset, high word = stride | version.
-    // Every operand sits at a compile-time offset inside S, so ONE register (the low word of S itself) + immediates
-    // addresses them all (the 14-bit address field cannot carry: shared memory ends below 2^18 bytes).
-    const uint32_t s_lo = ((ptx::smem_u32(&S) & 0x3FFFFu) >> 4) | ((kLbo >> 4) << 16);
+    const uint64_t a_const_desc = ptx::make_smem_desc(ptx::smem_u32(S.a_const), kLbo, kSbo);
+    const uint32_t res = ptx::smem_u32(S.resident);
+    // descriptor words, computed once: low word = address field | leading-byte offset, high word = stride | version
+    auto lo_word = [](uint32_t addr) { return ((addr & 0x3FFFFu) >> 4) | ((kLbo >> 4) << 16); };
     const uint32_t dhi = (kSbo >> 4) | (1u << 14);
-    constexpr uint32_t oRing16 = offsetof(Smem, wring) / 16, oBias16 = offsetof(Smem, wbias) / 16;
-    constexpr uint32_t oRes16 = offsetof(Smem, resident) / 16, oAc16 = offsetof(Smem, a_const) / 16;
-    static_assert(offsetof(Smem, wring) % 16 == 0 && offsetof(Smem, wbias) % 16 == 0 && offsetof(Smem, resident) % 16 == 0 &&
-                  offsetof(Smem, a_const) % 16 == 0, "operand images are 16-byte aligned inside S");
+    const uint32_t ring_lo = lo_word(ptx::smem_u32(&S.wring[t][0][0]));
+    const uint64_t bias_desc = ptx::make_smem_desc(ptx::smem_u32(&S.wbias[t][0]), kLbo, kSbo);
+    const uint32_t r6_lo = lo_word(res + rB6), r13_lo = lo_word(res + rB13);
+    const uint64_t r6_bias_desc = ptx::make_smem_desc(res + rB6Bias, kLbo, kSbo);
+    const uint64_t r0_desc0 = ptx::make_smem_desc(res + rB0, kLbo, kSbo);
+    const uint64_t r0_desc1 = ptx::make_smem_desc(res + rB0 + kKStepBytes, kLbo, kSbo);
+    const uint64_t r7_desc = ptx::make_smem_desc(res + rB7, kLbo, kSbo);
     constexpr uint32_t kSlot16 = 2 * kHalfBytes / 16, kLoOff16 = kHalfBytes / 16, kK128 = kKStepBytes / 16, kK16 = kKStep16 / 16;
     auto wait_bar = [&](uint64_t *bar, uint32_t parity) {
       while (!__all_sync(full, ptx::mbar_try_wait(bar, parity))) {
@@ -453,18 +425,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
 #pragma unroll 1
       for (int s = 0; s < kNStages; ++s, ++k) {
         const bool ring = ring_stage(s);
-        // the descriptor words of this stage, re-derived from s_lo behind an opaque copy: hoisted out of the loop
-        // they would be a dozen live registers in a warp that runs on kRegsEngine
-        uint32_t sl = s_lo;
-        asm volatile("" : "+r"(sl));
-        const uint32_t ring_lo = sl + oRing16 + (uint32_t)t * (4 * kHalfBytes / 16);
-        const uint64_t a_const_desc = ptx::desc_from_words(sl + oAc16, dhi);
-        const uint64_t bias_desc = ptx::desc_from_words(sl + oBias16 + (uint32_t)t * (kBiasBytes / 16), dhi);
-        const uint32_t r6_lo = sl + oRes16 + rB6 / 16, r13_lo = sl + oRes16 + rB13 / 16;
-        const uint64_t r6_bias_desc = ptx::desc_from_words(sl + oRes16 + rB6Bias / 16, dhi);
-        const uint64_t r0_desc0 = ptx::desc_from_words(sl + oRes16 + rB0 / 16, dhi);
-        const uint64_t r0_desc1 = ptx::desc_from_words(sl + oRes16 + (rB0 + kKStepBytes) / 16, dhi);
-        const uint64_t r7_desc = ptx::desc_from_words(sl + oRes16 + rB7 / 16, dhi);
         const uint32_t d_t = tmem_u + (k & 1u) * 128u;             // D of this stage
         const uint32_t a_reg = tmem_u + ((k & 1u) ^ 1u) * 128u;    // A: in place in the previous stage's D region
         wait_bar(&S.a_ready[t][0], apar0);
@@ -518,87 +478,22 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         tr.rec(2000 + 100 * t + s);
       }
     }
-  } else if (warp >= 8) {
-    // ===== assisting epilogue warpgroups: columns 64..127 of every 128-wide epilogue ========================
-    // Thread (slot t, row) converts chunks 2, 3 of D into the second K-half of the next stage's A operand while the
-    // star-owning thread of the same row converts chunks 0, 1: the operand is complete after half an epilogue and
-    // both halves of the next stage's MMAs are issued back to back.  It keeps no per-star state: the ReLU sign
-    // words of its chunks are its own (written forward, read backward), and the row maximum that fixes the
-    // power-of-two scale of a backward stage is exchanged with the owner through staging rows kXchRow...
-    const int t = (warp - 8) >> 2;
-    const int row = (warp & 3) * 32 + lane;
-    const uint32_t t_base = tmem + (((uint32_t)((warp & 3) * 32)) << 16) + (uint32_t)t * 256u;
-    const float inv_wscale = 1.0f / L.tc.w_scale;
-    uint32_t *mask = &S.mask[0][t * 128 + row];
-    float *xcol = &S.stage[kXchRow][t * 128 + row];
-    auto publish_a = [&](int c) {
-      ptx::tmem_wait_st();
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&S.a_ready[t][c]);
-    };
-    long long it = 0;
-    const long long my_iters = slot_iters(t);
-    for (long long p = 0; p < my_iters; ++p) {
-#pragma unroll 1
-      for (int s = 0; s < kNStages; ++s, ++it) {
-        // every phase of d_ready is waited for, also the stages without a wide epilogue (6, 13): a parity wait can
-        // only tell adjacent phases apart
-        ptx::mbar_wait(&S.d_ready[t], (uint32_t)(it & 1));
-        ptx::tc_fence_after();
-        const uint32_t d_base = t_base + (uint32_t)((it & 1) * 128);
-        if (L.tc.half_k) {  // 64-wide network: columns 64..127 do not exist; keep the barrier protocol only
-          if (s <= 5 || (s >= 7 && s <= 12)) publish_a(1);
-        } else if (s <= 5) {
-          uint32_t *mk = mask + s * 4 * 256;
-          for_chunk_pair<false>(d_base, 2, [&](const uint32_t (&r)[32], int c) {
-            mk[c * 256] = sign_word(r);
-            fwd_chunk<8>(r, inv_wscale, d_base, c);
-          });
-          publish_a(1);
-        } else if (s >= 7 && s <= 12) {
-          const int xo = 2 * ((s - 1) & 1) * kStageStride;
-          const float amax = fmaxf(xcol[xo], xcol[xo + kStageStride]);
-          const float f = pow2_scale(amax * S.small[oGain + (s - 7)]) * 32.0f;
-          float mx = 0.0f;
-          const uint32_t *mk = mask + (12 - s) * 4 * 256;
-          for_chunk_pair<false>(d_base, 2, [&](const uint32_t (&r)[32], int c) {
-#pragma unroll
-            for (int e = 0; e < 32; e += 2)
-              mx = fmaxf(mx, fmaxf(fabsf(__uint_as_float(r[e])), fabsf(__uint_as_float(r[e + 1]))));
-            bwd_chunk<8>(r, f, mk[c * 256], d_base, c);
-          });
-          if (s < 12) xcol[(2 * (s & 1) + 1) * kStageStride] = mx * f;
-          publish_a(1);
-        }
-      }
-    }
   } else {
-    // ===== star-owning epilogue warpgroups: one thread = one star ========================================
+    // ===== epilogue warpgroups: one thread = one star ===================================================
     const int t = warp >> 2;                   // tile slot within the pair
     const int row = (warp & 3) * 32 + lane;    // TMEM lane == row of the tile
     const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
     // TMEM of a tile: two 128-column regions.  Stage k (counted over the tile's whole life, `it`) accumulates D
     // into region k & 1; its epilogue converts D into the next stage's A operand IN PLACE, so stage k + 1 reads A
-    // from region k & 1 and accumulates into the other one.  This thread converts chunks 0, 1 (the first K-half of
-    // the next operand), the assisting thread of the row chunks 2, 3 at the same time.
+    // from region k & 1 and accumulates into the other one.  Because A appears chunk by chunk, the MMAs of the
+    // next stage start on K-chunk c while the epilogue is still converting chunk c + 1.
     const uint32_t t_base = tmem + lane_base + (uint32_t)t * 256u;
-    // per-star state lives in this branch only: nothing of it is carried through the other roles' registers
-    const HyperVals hv = S.hv;
-    HyperAcc acc{};
-    if (grid_in_smem) {  // table axes and their lookup tables: the shared-memory copies
-      int off = 0;
-#pragma unroll
-      for (int d = 0; d < 4; ++d) {
-        gl.pts[d] = S.grid_pts + off;
-        gl.lut[d] = S.grid_lut[d];
-        off += gl.shape[d];
-      }
-    }
     const float *sm = S.small;
     const float inv_fwd = 1.0f / (kActScale * L.tc.w_scale);
     const float inv_wscale = 1.0f / L.tc.w_scale;
     uint32_t *mask = &S.mask[0][tid];  // sign word of chunk c of hidden layer h at mask[(h * 4 + c) * 256]
+    // chunk pairs per 128-wide epilogue: a 64-wide network (operator modes only) has columns 0..63 only
+    const int ncc = (NET && L.tc.half_k) ? 1 : 2;
     // hand the A operand to the MMA warp: all tcgen05.st of this warp done, then one elected arrive
     // (one barrier per K-half: a half's next phase belongs to the next stage, which cannot begin before the MMA
     // warp has consumed this one, so the producer can never run two phases ahead of the consumer's parity)
@@ -622,7 +517,6 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
     // observations out of the column, the observations of tile p once its priors have taken the sites.  Nothing
     // but the thread itself touches the column, so cp.async.wait_all is the only synchronisation.
     float *col = &S.stage[0][tid];
-    float *xcol = &S.stage[kXchRow][tid];  // row maxima exchanged with the assisting thread (backward stages)
     auto stage = [&](const StageList &l, long long ii) {
       if (NET || ii >= n) return;
       const int cnt = l.n;
@@ -698,11 +592,12 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         if (s <= 5) {
           // ---- pre-activations of hidden layer s (bias already in D) -> sign word, ReLU -> next A operand ----
           uint32_t *mk = mask + s * 4 * 256;
-          for_chunk_pair<true>(d_base, 0, [&](const uint32_t (&r)[32], int c) {
+          for_chunks(d_base, ncc, [&](const uint32_t (&r)[32], int c) {
             mk[c * 256] = sign_word(r);
             fwd_chunk(r, inv_wscale, a_base, c);
+            if (c & 1) publish_a(c >> 1);  // K-half c >> 1 of the next stage's A operand is complete
           });
-          publish_a(0);  // K-half 0 of the next stage's A operand is complete (half 1: the assisting warpgroup)
+          if (ncc == 1) publish_a(1);  // 64-wide network: the second K-half does not exist (protocol only)
         } else if (s == 6) {
           // ---- emulator outputs -> predict + likelihood -> cotangent of the outputs -> A operand of stage 7 ----
           uint32_t r8[8];
@@ -766,29 +661,24 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
             split2(g_y[2] * f, g_y[3] * f, h23, l23);
             const uint32_t ag[8] = {h01, h23, l01, l23, h01, h23, 0u, 0u};
             ptx::tmem_st8(a_base, ag);
-            xcol[0] = amax;            // stage 7 reads [parity 0][owner, assistant]
-            xcol[kStageStride] = 0.0f;
           }
         } else if (s <= 12) {
           // ---- cotangent of hidden layer h = 12 - s: re-scale, ReLU mask, next A operand --------------------
           // |D| <= amax * (s_w * G) with G = the largest row L1 norm of this stage's B image, so the scale is
           // known BEFORE D is read (one pass); the exact row maximum is gathered for the next stage.
           const int h = 12 - s;
-          {  // row maximum of this stage's A operand: the owner's and the assistant's halves of the previous epilogue
-            const int xo = 2 * ((s - 1) & 1) * kStageStride;
-            amax = L.tc.half_k ? xcol[xo] : fmaxf(xcol[xo], xcol[xo + kStageStride]);  // (64-wide network: no assistant half)
-          }
           const float f = pow2_scale(amax * sm[oGain + (s - 7)]) * 32.0f;  // f * |D| < 2^15
           float mx = 0.0f;
           const uint32_t *mk = mask + h * 4 * 256;
-          for_chunk_pair<true>(d_base, 0, [&](const uint32_t (&r)[32], int c) {
+          for_chunks(d_base, ncc, [&](const uint32_t (&r)[32], int c) {
 #pragma unroll
             for (int e = 0; e < 32; e += 2)
               mx = fmaxf(mx, fmaxf(fabsf(__uint_as_float(r[e])), fabsf(__uint_as_float(r[e + 1]))));
             bwd_chunk(r, f, mk[c * 256], a_base, c);
+            if (c & 1) publish_a(c >> 1);
           });
-          if (s < 12) xcol[2 * (s & 1) * kStageStride] = mx * f;
-          publish_a(0);
+          if (ncc == 1) publish_a(1);
+          amax = mx * f;
           un = un / f * inv_wscale;
         } else {
           // ---- cotangent of the (normalised) emulator inputs -> chain rule to the sites -> gradient stores ------
@@ -819,20 +709,14 @@ __global__ void __launch_bounds__(kThreads, 1) potential_tc_kernel(const __grid_
         }
       }
     }
-    if (MODE == M_POTENTIAL) warp_partials_to_smem(acc, S.red);  // warps 0..7: the only ones that hold sums
   }
 
   // ---- teardown + reduction (all threads) -----------------------------------------------------------
-  // back to the launch-time register budget: the code below is shared by all roles (and calls a function)
-  if (warp >= 16) ptx::setmaxnreg_inc<kRegsLaunch>();
-  else if (warp >= 8) ptx::setmaxnreg_inc<kRegsLaunch>();
-  else ptx::setmaxnreg_dec<kRegsLaunch>();
   ptx::tc_fence_before();
   __syncthreads();
   ctr.rec(3);
-  if (warp == 16) ptx::tmem_dealloc<kTmemCols>(tmem);
-  if (MODE == M_POTENTIAL)
-    block_reduce_finalize_tail(m, S.hv, 8, S.red, L.partials, L.counter, L.out6, L.grad_hyper, L.px);
+  if (warp == 8) ptx::tmem_dealloc<kTmemCols>(tmem);
+  if (MODE == M_POTENTIAL) block_reduce_finalize(m, hv, acc, S.red, L.partials, L.counter, L.out6, L.grad_hyper, L.px);
   ctr.rec(4);
 }
 
