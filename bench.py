@@ -483,8 +483,9 @@ def run_b200(args):
                          "frac": achieved / bf16_peak, "traffic": traffic,
                          "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, ncu --set full)",
                          "traffic_source": None if traffic is None else
-                         f"committed ncu capture profiles/potential_ncu.json @ {git_sha('profiles/potential_ncu.json')} "
-                         "(a constant of that capture, not a measurement of this run)",
+                         "committed ncu capture profiles/potential_ncu.json"
+                         + (f" @ {git_sha('profiles/potential_ncu.json')}" if git_sha('profiles/potential_ncu.json') else "")
+                         + " (a constant of that capture, not a measurement of this run)",
                          "algorithmic_bytes": alg_bytes,
                          "kernel": "potential_tc_kernel" if args.engine == "tcgen05" else "potential_ffma_kernel",
                          "kernel_ms": kern, "stars_per_launch": stars_local, "flop_per_star": FLOP_PER_STAR,
