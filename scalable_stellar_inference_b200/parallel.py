@@ -417,3 +417,69 @@ class ZeroCopyHostPotential:
             dist.all_reduce(self._sum, group=self.group)
             tot = self._sum.cpu().numpy()
         return float(tot[0]), tot[1:6].copy(), self.grad_view
+
+
+class InterleavedHostPotential:
+    """End-to-end evaluation through HOST buffers for SEVERAL independent chains: chain c's host -> device copy, its
+    kernel and its device -> host copy run on three streams, so that while the SMs evaluate one chain the copy engines
+    bring the next chain's sites in and take the previous chain's gradient out.  Every step still moves its own inputs
+    from page-locked host memory and its own results back (h2d_bytes / d2h_bytes per step), but a step costs
+    ~max(kernel, copies) instead of the kernel slowed down by its own PCIe reads (``ZeroCopyHostPotential``: one chain,
+    the kernel reads host memory itself, 0.2 ms slower at 1 M stars).  Steps of ONE chain depend on each other, steps
+    of different chains do not -- the reference itself runs 4-10 chains (scripts/model_star.py:78) -- so a host-side
+    sampler with >= 2 chains per GPU keeps the device busy this way.  One libcsi handle serves all chains (same
+    observations); ``z_pin[c]`` / ``grad_pin[c]`` / ``out_pin[c]`` are the chains' page-locked buffers.
+    Needs the in-kernel peer exchange when sharded."""
+
+    def __init__(self, model, chains=2):
+        import torch
+        self.torch, self.model, self.chains = torch, model, chains
+        self.device = torch.device("cuda", model.device)
+        n = model.flat_size
+        mk = lambda shape, dt, pin: (torch.zeros(shape, dtype=dt).pin_memory() if pin  # noqa: E731
+                                     else torch.zeros(shape, dtype=dt, device=self.device))
+        self.z_pin = [mk(n, torch.float32, True) for _ in range(chains)]
+        self.grad_pin = [mk(n, torch.float32, True) for _ in range(chains)]
+        self.out_pin = [mk(8, torch.float64, True) for _ in range(chains)]
+        self.z_dev = [mk(n, torch.float32, False) for _ in range(chains)]
+        self.grad_dev = [mk(n, torch.float32, False) for _ in range(chains)]
+        self.out_dev = [mk(8, torch.float64, False) for _ in range(chains)]
+        self.s_in, self.s_k, self.s_out = (torch.cuda.Stream(self.device) for _ in range(3))
+        self.ev_in = [torch.cuda.Event() for _ in range(chains)]
+        self.ev_k = [torch.cuda.Event() for _ in range(chains)]
+        self.ev_out = [torch.cuda.Event() for _ in range(chains)]
+        self._used = [False] * chains
+        self.h2d_bytes, self.d2h_bytes = n * 4, n * 4 + 6 * 8
+        self.launches = 0
+
+    def load(self, c, z_flat):
+        self.z_pin[c].copy_(self.torch.as_tensor(np.asarray(z_flat, np.float32)))
+
+    def submit(self, c):
+        """Queue one evaluation of chain c (its current ``z_pin[c]``); returns at once."""
+        torch = self.torch
+        with torch.cuda.stream(self.s_in):
+            if self._used[c]:
+                self.s_in.wait_event(self.ev_k[c])       # the previous kernel of this chain has read z_dev[c]
+            self.z_dev[c].copy_(self.z_pin[c], non_blocking=True)
+            self.ev_in[c].record(self.s_in)
+        with torch.cuda.stream(self.s_k):
+            self.s_k.wait_event(self.ev_in[c])
+            if self._used[c]:
+                self.s_k.wait_event(self.ev_out[c])      # grad_dev[c] / out_dev[c] have been copied out
+            self.model.potential_device(self.z_dev[c].data_ptr(), self.out_dev[c].data_ptr(), self.grad_dev[c].data_ptr(),
+                                        self.s_k.cuda_stream)
+            self.ev_k[c].record(self.s_k)
+        with torch.cuda.stream(self.s_out):
+            self.s_out.wait_event(self.ev_k[c])
+            self.grad_pin[c].copy_(self.grad_dev[c], non_blocking=True)
+            self.out_pin[c].copy_(self.out_dev[c], non_blocking=True)
+            self.ev_out[c].record(self.s_out)
+        self._used[c] = True
+        self.launches += 1
+
+    def result(self, c):
+        """Wait for chain c's last evaluation: (U, dU/dhyper[5], gradient in ``grad_pin[c]``)."""
+        self.ev_out[c].synchronize()
+        o = self.out_pin[c].numpy()
+        return float(o[0]), o[1:6].copy(), self.grad_pin[c]
