@@ -100,7 +100,8 @@ def test_posterior_of_device_sampler_matches_oracle_posterior():
     evaluation -- a 256-star fixture would take a working day), so their summary is a committed fixture
     (tests/golden/posterior_hier64_seis.json: mean, sd and ESS of the 5 hyper-parameters and of the sites of 6 stars,
     written by tools/gen_posterior_fixture.py with the host-recursive nuts.NUTS over oracle.model.potential_and_grad).
-    Means must agree within Monte-Carlo standard error (both chains' ESS), spreads within 25 %."""
+    Means must agree within Monte-Carlo standard error (both chains' ESS), spreads within 25 % where both runs have
+    ESS >= 200 for the coordinate."""
     path = os.path.join(GOLDEN, "posterior_hier64_seis.json")
     if not os.path.exists(path):
         pytest.skip("fixture not generated yet")
@@ -125,7 +126,11 @@ def test_posterior_of_device_sampler_matches_oracle_posterior():
         dev = abs(mean - mean_ref[k]) / mcse
         bad += dev > 3.5
         assert dev < 6.0, (k, mean, mean_ref[k], mcse)
-        assert 0.75 < sd / sd_ref[k] < 1.33, (k, sd, sd_ref[k])
+        # a sample sd from ESS effective draws is itself uncertain by ~ 1/sqrt(2 ESS) (x2-3 for the heavy-tailed
+        # funnel coordinates): 25 % only where both runs resolved the coordinate (the fixture's ESS of precision_a
+        # is 38, of mu_a 20), a gross-failure guard elsewhere
+        lo_r, hi_r = (0.75, 1.33) if min(ess, ess_ref[k]) >= 200 else (0.4, 2.5)
+        assert lo_r < sd / sd_ref[k] < hi_r, (k, sd, sd_ref[k], ess, ess_ref[k])
         if k < nh:   # the oracle's own chains reach r-hat 1.16 on mu_a at this length: a gross-failure guard only
             assert split_rhat(x[:, :, k]) < 1.35
     assert bad <= max(1, x.shape[2] // 20)
