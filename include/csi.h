@@ -212,6 +212,19 @@ int csi_leapfrog_post(csi_handle *h, const float *r_half, const float *grad, con
 int csi_uturn(csi_handle *h, const float *r_left, const float *r_right, const float *r_sum, const float *inv_mass,
               double *dots4, void *stream);
 
+/* csi_uturn for callers that may not allocate (code under CUDA-graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.  Same arguments,
+ * same launch and same sums as csi_uturn, but the block partials and the ticket of the grid reduction live in a
+ * file-scope device array of CSI_STATIC_SCRATCH_BYTES (1024 blocks x 25 doubles + a 256-byte ticket line) that
+ * every GPU loading the library holds until the process exits, so the call performs no cudaMalloc / cudaFree.
+ * Vectors longer than CSI_UTURN_STATIC_MAX_LEN elements are refused with CSI_EINVAL.  All calls on a device share
+ * the array: calls that overlap on the GPU (different streams, or a second handle on the same device) race --
+ * serialise them, or use csi_uturn, whose scratch is per handle. */
+#define CSI_STATIC_SCRATCH_BYTES 205056
+#define CSI_UTURN_STATIC_MAX_LEN (1 << 24)
+int csi_uturn_static(csi_handle *h, const float *r_left, const float *r_right, const float *r_sum,
+                     const float *inv_mass, double *dots4, void *stream);
+
 /* ---- the sampler itself: No-U-Turn transitions with the tree logic on the device ----------------------------------
  * Replaces numpyro.infer.NUTS / MCMC as driven by scripts/model_star.py:132-155 (multinomial NUTS, iterative
  * sub-tree building with checkpointed U-turn tests, biased progressive sampling; numpyro/infer/hmc_util.py).

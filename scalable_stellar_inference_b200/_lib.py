@@ -66,6 +66,7 @@ class NutsStats(C.Structure):
 
 
 PEER_SLOT_DOUBLES = 32
+UTURN_STATIC_MAX_LEN = 1 << 24
 
 
 _PROTOS = {
@@ -83,6 +84,7 @@ _PROTOS = {
     "csi_leapfrog_pre": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
     "csi_leapfrog_post": (C.c_int, [C.c_void_p] * 5 + [C.c_float] + [C.c_void_p] * 4),
     "csi_uturn": (C.c_int, [C.c_void_p] * 7),
+    "csi_uturn_static": (C.c_int, [C.c_void_p] * 7),
     "csi_nuts_create": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double, C.c_uint64,
                                   C.c_int64, C.c_int64, C.POINTER(C.c_void_p)]),
     "csi_nuts_destroy": (None, [C.c_void_p]),

@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <limits>
+#include <mutex>
 
 #include "csi_internal.h"
 
@@ -753,3 +754,60 @@ extern "C" int csi_time_potential(csi_handle *h, const float *z_dev, double *out
 }
 
 #include "csi_nuts.cuh"  // NUTS leapfrog / U-turn vector kernels (csi_leapfrog_pre, csi_leapfrog_post, csi_uturn)
+
+// ---------------------------------------------------------------------------------------------------------------
+// csi_uturn_static: csi_uturn for callers that may not allocate (no counterpart in the reference).
+// The block partials and the ticket of the fixed-order grid reduction live in a
+// file-scope device array instead of the handle's cudaMalloc'ed scratch, so the call does no cudaMalloc / cudaFree.
+// Every GPU that loads the library holds the array (CSI_STATIC_SCRATCH_BYTES) until the process exits, and every
+// call on a device shares it: calls that overlap on the GPU race.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr int kStaticBlocks = 1024;                               // >= 4 CTAs per SM on a B200 (592)
+constexpr int kStaticTicketDoubles = 32;                          // the ticket gets its own 256 bytes at the end
+constexpr size_t kStaticDoubles = (size_t)kStaticBlocks * csi::nuts::kNV + kStaticTicketDoubles;
+static_assert(kStaticDoubles * sizeof(double) == CSI_STATIC_SCRATCH_BYTES, "csi.h states the size of the array");
+constexpr int kStaticMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) double g_uturn_static_scratch[kStaticDoubles];
+
+// In host code `g_uturn_static_scratch` is only a stand-in for the symbol: the device address has to be asked for,
+// once per device, with that device current.
+static double *g_uturn_static_ptr[kStaticMaxDevices];
+static std::mutex g_uturn_static_mu;
+
+static int uturn_static_scratch(int device, double **out) {
+  if (device < 0 || device >= kStaticMaxDevices) return fail(CSI_EINVAL, "csi_uturn_static: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_uturn_static_mu);
+  if (!g_uturn_static_ptr[device]) {
+    double *p = nullptr;
+    CK(cudaGetSymbolAddress((void **)&p, g_uturn_static_scratch));   // the caller checked that `device` is current
+    if (!p) return fail(CSI_ECUDA, "csi_uturn_static: cudaGetSymbolAddress returned a null address");
+    g_uturn_static_ptr[device] = p;
+  }
+  *out = g_uturn_static_ptr[device];
+  return CSI_OK;
+}
+
+extern "C" int csi_uturn_static(csi_handle *h, const float *r_left, const float *r_right, const float *r_sum,
+                                const float *inv_mass, double *dots4, void *stream) {
+  if (!h || !r_left || !r_right || !r_sum || !inv_mass || !dots4) return fail(CSI_EINVAL, "null argument");
+  if (h->n_local < 1) return fail(CSI_ESTATE, "csi_set_data has not been called");
+  if (int rcd = check_device(h)) return rcd;
+  const long long n = h->stage_len;
+  if (n > (long long)CSI_UTURN_STATIC_MAX_LEN)
+    return fail(CSI_EINVAL, "csi_uturn_static: vector length " + std::to_string(n) + " exceeds CSI_UTURN_STATIC_MAX_LEN (" +
+                                std::to_string((long long)CSI_UTURN_STATIC_MAX_LEN) + "); use csi_uturn");
+  double *scratch = nullptr;
+  if (int rcs = uturn_static_scratch(h->device, &scratch)) return rcs;
+  unsigned int *ticket = reinterpret_cast<unsigned int *>(scratch + (size_t)kStaticBlocks * csi::nuts::kNV);
+  // the array keeps the last call's contents: the partials are overwritten before they are read, the ticket must
+  // start at zero (the finalising block resets it, but a launch that was aborted would not have)
+  CK(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), (cudaStream_t)stream));
+  const int grid = std::min(csi::nuts::grid_for(h, n), kStaticBlocks);   // same grid as csi_uturn -> same sums
+  csi::nuts::uturn_kernel<<<grid, csi::nuts::kBlock, 0, (cudaStream_t)stream>>>(
+      n, h->n_hyper, r_left, r_right, r_sum, inv_mass, dots4, scratch, ticket);
+  CK(cudaGetLastError());
+  return CSI_OK;
+}
